@@ -1,0 +1,95 @@
+// Layout constants shared by the deformation-MLP kernels (forward, input-gradient chain, weight gradient).
+//
+// Network (utils/time_utils.py:56-201): PE(xyz) 63 | t-feature (timenet output 30, or PE(t) 21) -> "pe"
+// block of pe_dim = 93 / 84 columns padded to 96; 8 layers of width 256, layer 5 takes [pe | h4];
+// heads 256 -> up to 13 outputs padded to 16.
+//
+// One tile = 128 points.  All matrix operands are panelised SWIZZLE_128B images (umma.cuh).
+#pragma once
+#include "common.cuh"
+#include "umma.cuh"
+
+namespace d3g {
+
+constexpr int kRows = 128;                 // points per tile
+constexpr uint32_t kPanelBytes = 16384;    // 128 rows x 32 fp32
+constexpr uint32_t kPeBytes = 3 * kPanelBytes;
+constexpr uint32_t kHBytes = 8 * kPanelBytes;  // one 128x256 activation tile image
+constexpr uint32_t kStageBytes = 32768;    // one weight stage: 256 rows x 32 k
+constexpr int kFwdStages = 63;             // L0:3 L1-4:32 L5pe:3 L5h:8 L6-7:16 heads:1
+constexpr int kBwdStages = 57;             // headsT:1 + 7 layers x 8
+constexpr int kBiasFloats = 8 * 256 + 16;
+constexpr size_t kFwdBytes = (size_t)62 * kStageBytes + 16384;
+constexpr size_t kBiasOff = kFwdBytes;
+constexpr size_t kBiasBytes = 8448;  // kBiasFloats*4 rounded up to 256
+constexpr size_t kBwdOff = kBiasOff + kBiasBytes;
+constexpr size_t kBwdBytes = (size_t)kBwdStages * kStageBytes;
+constexpr size_t kPackedBytes = kBwdOff + kBwdBytes;
+
+// forward stage -> (layer id, k panel).  layer ids: 0..7 trunk (5 = h part of the skip layer),
+// 8 = pe part of layer 5, 9 = heads.
+__host__ __device__ inline void fwd_stage_info(int st, int& layer, int& kpanel) {
+  if (st < 3) { layer = 0; kpanel = st; }
+  else if (st < 35) { layer = 1 + (st - 3) / 8; kpanel = (st - 3) % 8; }
+  else if (st < 38) { layer = 8; kpanel = st - 35; }
+  else if (st < 46) { layer = 5; kpanel = st - 38; }
+  else if (st < 62) { layer = 6 + (st - 46) / 8; kpanel = (st - 46) % 8; }
+  else { layer = 9; kpanel = 0; }
+}
+// backward stage order: headsT, then layers 7,6,5(h part),4,3,2,1 transposed
+__host__ __device__ inline void bwd_stage_info(int st, int& layer, int& kpanel) {
+  if (st == 0) { layer = 9; kpanel = 0; }
+  else { layer = 7 - (st - 1) / 8; kpanel = (st - 1) % 8; }
+}
+
+// ---- workspace layout -------------------------------------------------------------------------
+struct MlpWs {
+  int32_t* status;     // [0] abort flag
+  float* tfeat;        // [rows_t, 32]   time feature fed into pe columns 63..
+  float* thidden;      // [rows_t, 256]  timenet hidden (post-ReLU), blender only
+  uint8_t* pe_img;     // [tiles] x 48 KB
+  uint8_t* h_img;      // [8][tiles] x 128 KB   post-ReLU activations h_0..h_7 (tf32-rounded)
+  uint32_t* mask;      // [8][tiles][8 chunks][128 rows]  bit j = (h[row][chunk*32+j] > 0)
+  float* heads_out;    // [tiles*128, 16] head pre-outputs (incl. bias)
+  uint8_t* dz_img;     // [8][tiles] x 128 KB   dL/d(pre-activation) tiles, written by backward
+  uint8_t* dout_img;   // [tiles] x 16 KB       head cotangents as a 32-column panel
+  float* partial;      // weight-gradient split-K partials
+  size_t partial_floats;
+  size_t total;
+};
+
+constexpr int kWgradSlots = 160;                 // upper bound on split-K work items
+constexpr size_t kWgradSlotFloats = 128 * 384;   // 128 out-features x (352 in + 16 bias + pad)
+
+inline MlpWs mlp_ws_view(void* base, int64_t rows, bool save) {
+  MlpWs w;
+  char* p = (char*)base;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { char* r = p + off; off += align_up(bytes, 1024); return r; };
+  size_t tiles = (size_t)((rows + kRows - 1) / kRows);
+  if (tiles == 0) tiles = 1;
+  size_t r = (size_t)(rows > 0 ? rows : 1);
+  w.status = (int32_t*)take(1024);
+  w.tfeat = (float*)take(r * 32 * 4);
+  w.thidden = (float*)take(save ? r * 256 * 4 : 1024);
+  if (save) {
+    w.pe_img = (uint8_t*)take(tiles * kPeBytes);
+    w.h_img = (uint8_t*)take(8 * tiles * (size_t)kHBytes);
+    w.mask = (uint32_t*)take(8 * tiles * 8 * 128 * 4);
+    w.heads_out = (float*)take(tiles * 128 * 16 * 4);
+    w.dz_img = (uint8_t*)take(8 * tiles * (size_t)kHBytes);
+    w.dout_img = (uint8_t*)take(tiles * (size_t)kPanelBytes);
+    w.partial_floats = (size_t)kWgradSlots * kWgradSlotFloats;
+    w.partial = (float*)take(w.partial_floats * 4);
+  } else {
+    w.pe_img = w.h_img = w.dz_img = w.dout_img = nullptr;
+    w.mask = nullptr; w.heads_out = nullptr; w.partial = nullptr; w.partial_floats = 0;
+  }
+  w.total = off;
+  return w;
+}
+
+int check_cfg(const d3g_mlp_config* cfg);
+int num_sms();
+
+}  // namespace d3g

@@ -1,0 +1,594 @@
+// Fused deformation-MLP forward for sm_100a (tcgen05 / TMEM / bulk-copy).
+//
+// Replaces DeformNetwork(.Baseline).forward, utils/time_utils.py:102-127 / :176-201: positional
+// encoding, 8x256 trunk with the skip at layer 5, heads and the optional se(3) exponential map run in
+// ONE persistent kernel.  Per 128-point tile:
+//   * the positional-encoding block (96 columns) is built in shared memory once and feeds layer 0 and
+//     the skip layer as an smem A operand;
+//   * every other activation lives ONLY in tensor memory: the fp32 accumulator of layer l (TMEM half
+//     l&1, 256 columns) is bias+ReLU'd in place by the epilogue warps (tcgen05.ld -> regs ->
+//     tcgen05.st, rounded to tf32) and is then consumed directly as the TMEM A operand of layer l+1,
+//     whose accumulator is the other half.  Activations never touch shared memory or HBM in inference;
+//   * weights stream from the packed image (L2-resident, 2 MB) through a 5-stage bulk-copy ring
+//     (cp.async.bulk + mbarrier expect_tx), 32 KB = 256 outputs x 32 k per stage;
+//   * the epilogue hands the next layer its A operand 32 columns at a time (8 mbarriers), so the MMA
+//     of layer l+1 starts while the epilogue of layer l is still draining.
+// Warp roles: 0-7 epilogue/PE (warp w owns TMEM lanes 32*(w&3).., column chunks of parity w>>2),
+// 8 weight producer, 9 MMA issuer + TMEM owner.
+#include <math.h>
+
+#include "mlp_common.cuh"
+
+namespace d3g {
+
+constexpr int kNumStages = 5;
+constexpr int kFwdThreads = 320;
+
+struct FwdSmem {
+  // offsets inside dynamic shared memory (after 1024-alignment)
+  static constexpr uint32_t pe = 0;
+  static constexpr uint32_t stages = kPeBytes;
+  static constexpr uint32_t bias = stages + kNumStages * kStageBytes;
+  static constexpr uint32_t bars = bias + kBiasFloats * 4 + 64;  // 8-byte aligned
+  static constexpr uint32_t total = bars + 256;
+};
+static_assert(FwdSmem::bars % 8 == 0, "barrier alignment");
+
+struct MlpFwdArgs {
+  const uint8_t* wfwd;
+  const float* bias;
+  const float* xyz;
+  int64_t rows;
+  int tiles;
+  const float* tfeat;
+  int64_t tfeat_stride;  // 0 (uniform t) or 32
+  int pe_dim, t_dim;
+  int is_6dof, heads;
+  int save;
+  uint8_t* pe_img;
+  uint8_t* h_img;
+  uint32_t* mask;
+  float* heads_out;
+  float* d_xyz;
+  float* d_rot;
+  float* d_scale;
+  int* abort_flag;
+};
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* sPE = smem + FwdSmem::pe;
+  uint8_t* sStage = smem + FwdSmem::stages;
+  float* sBias = (float*)(smem + FwdSmem::bias);
+  uint64_t* bars = (uint64_t*)(smem + FwdSmem::bars);
+  uint64_t* full = bars;                   // [kNumStages]
+  uint64_t* empty = bars + kNumStages;     // [kNumStages]
+  uint64_t* acc_full = bars + 2 * kNumStages;
+  uint64_t* pe_ready = acc_full + 1;
+  uint64_t* a_ready = pe_ready + 1;        // [8]
+  uint32_t* tmem_slot = (uint32_t*)(a_ready + 8);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  volatile int* abort_flag = a.abort_flag;
+
+  if (tid == 0) {
+    for (int i = 0; i < kNumStages; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(acc_full, 1);
+    mbar_init(pe_ready, 8);
+    for (int i = 0; i < 8; i++) mbar_init(&a_ready[i], 4);
+    fence_barrier_init();
+  }
+  if (warp == 9) tmem_alloc(tmem_slot, 512);
+  for (int i = tid; i < kBiasFloats; i += kFwdThreads) sBias[i] = a.bias[i];
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 8) {
+    // ================= weight producer =================
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      bool ok = true;
+      for (int tile = blockIdx.x; ok && tile < a.tiles; tile += gridDim.x) {
+        for (int st = 0; st < kFwdStages; st++) {
+          if (!mbar_wait(&empty[s], ph ^ 1, abort_flag)) { ok = false; break; }
+          uint32_t bytes = st == kFwdStages - 1 ? 16384u : kStageBytes;
+          mbar_arrive_expect_tx(&full[s], bytes);
+          bulk_g2s(sStage + (size_t)s * kStageBytes, a.wfwd + (size_t)st * kStageBytes, bytes, &full[s]);
+          if (++s == kNumStages) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 9) {
+    // ================= MMA issuer =================
+    if (lane == 0) {
+      const uint32_t idesc256 = make_idesc_tf32(128, 256, 0, 0);
+      const uint32_t idesc16 = make_idesc_tf32(128, 16, 0, 0);
+      int s = 0;
+      uint32_t ph = 0, pe_ph = 0, a_ph = 0;
+      bool ok = true;
+      auto wait_full = [&]() { return mbar_wait(&full[s], ph, abort_flag); };
+      auto release = [&]() { umma_commit(&empty[s]); if (++s == kNumStages) { s = 0; ph ^= 1; } };
+      for (int tile = blockIdx.x; ok && tile < a.tiles; tile += gridDim.x) {
+        if (!mbar_wait(pe_ready, pe_ph, abort_flag)) { ok = false; break; }
+        pe_ph ^= 1;
+        tc_fence_after();
+        // pe-fed part of a layer: A from shared memory (3 panels)
+        auto pe_part = [&](uint32_t d_col) {
+          for (int kc = 0; ok && kc < 3; kc++) {
+            if (!wait_full()) { ok = false; break; }
+            tc_fence_after();
+            uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes);
+            uint32_t sa = smem_u32(sPE) + kc * kPanelBytes;
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++)
+              umma_tf32_ss(tmem_base + d_col, make_smem_desc(sa + ks * 32, 16, 1024),
+                           make_smem_desc(sb + ks * 32, 16, 1024), idesc256, (kc | ks) != 0);
+            release();
+          }
+        };
+        // h-fed part: A from tensor memory, handed over 32 columns at a time
+        auto h_part = [&](uint32_t d_col, uint32_t a_col, bool accumulate_first) {
+          for (int kc = 0; ok && kc < 8; kc++) {
+            if (!mbar_wait(&a_ready[kc], a_ph, abort_flag)) { ok = false; break; }
+            if (!wait_full()) { ok = false; break; }
+            tc_fence_after();
+            uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes);
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++)
+              umma_tf32_ts(tmem_base + d_col, tmem_base + a_col + kc * 32 + ks * 8,
+                           make_smem_desc(sb + ks * 32, 16, 1024), idesc256,
+                           (accumulate_first || (kc | ks) != 0) ? 1u : 0u);
+            release();
+          }
+          a_ph ^= 1;
+        };
+        pe_part(0);                       // layer 0 -> half 0
+        if (!ok) break;
+        umma_commit(acc_full);
+        for (int l = 1; ok && l < 8; l++) {
+          uint32_t d_col = (l & 1) * 256, a_col = ((l - 1) & 1) * 256;
+          if (l == 5) {
+            pe_part(d_col);               // overlaps the epilogue of layer 4
+            if (!ok) break;
+            h_part(d_col, a_col, true);
+          } else {
+            h_part(d_col, a_col, false);
+          }
+          if (!ok) break;
+          umma_commit(acc_full);
+        }
+        if (!ok) break;
+        // heads: N = 16, A = h7 (half 1), D = half 0 columns 0..15, single 16 KB stage
+        {
+          bool have = false;
+          for (int kc = 0; ok && kc < 8; kc++) {
+            if (!mbar_wait(&a_ready[kc], a_ph, abort_flag)) { ok = false; break; }
+            if (!have) { if (!wait_full()) { ok = false; break; } have = true; }
+            tc_fence_after();
+            uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes) + kc * 2048;
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++)
+              umma_tf32_ts(tmem_base + 0, tmem_base + 256 + kc * 32 + ks * 8,
+                           make_smem_desc(sb + ks * 32, 16, 1024), idesc16, (kc | ks) != 0);
+          }
+          if (!ok) break;
+          a_ph ^= 1;
+          release();
+          umma_commit(acc_full);
+        }
+      }
+    }
+  } else {
+    // ================= PE + epilogue warps (256 threads) =================
+    const int q = warp & 3, chalf = warp >> 2;
+    const int row = q * 32 + lane;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+    uint32_t acc_ph = 0;
+    bool ok = true;
+    bool store_pending = false;
+    for (int tile = blockIdx.x; ok && tile < a.tiles; tile += gridDim.x) {
+      const int64_t grow = (int64_t)tile * kRows + row;
+      const bool live = grow < a.rows;
+      // ---- positional encoding block -> shared memory (K-major SW128 image, 3 panels) ----
+      if (store_pending) {  // previous tile's pe image is still being read by the bulk store
+        if (tid == 0) bulk_wait_read<0>();
+        named_bar_sync(1, 256);
+        store_pending = false;
+      }
+      {
+        float x[3] = {0.f, 0.f, 0.f};
+        if (live) { x[0] = a.xyz[3 * grow]; x[1] = a.xyz[3 * grow + 1]; x[2] = a.xyz[3 * grow + 2]; }
+        auto put = [&](int col, float v) { *(uint32_t*)(sPE + img_off(row, col, kPanelBytes)) = to_tf32(v); };
+        if (chalf == 0) {
+          put(0, x[0]); put(1, x[1]); put(2, x[2]);
+          for (int f = 0; f < 5; f++) {
+            float fr = (float)(1 << f);
+#pragma unroll
+            for (int d = 0; d < 3; d++) {
+              float sn, cs;
+              sincosf(x[d] * fr, &sn, &cs);
+              put(3 + 6 * f + d, sn);
+              put(3 + 6 * f + 3 + d, cs);
+            }
+          }
+        } else {
+          for (int f = 5; f < 10; f++) {
+            float fr = (float)(1 << f);
+#pragma unroll
+            for (int d = 0; d < 3; d++) {
+              float sn, cs;
+              sincosf(x[d] * fr, &sn, &cs);
+              put(3 + 6 * f + d, sn);
+              put(3 + 6 * f + 3 + d, cs);
+            }
+          }
+          const float* tf = a.tfeat + (live ? grow * a.tfeat_stride : 0);
+          for (int j = 0; j < 33; j++) put(63 + j, (live && j < a.t_dim) ? tf[j] : 0.f);
+        }
+      }
+      fence_proxy_async();
+      if (a.save) {
+        named_bar_sync(1, 256);
+        if (tid == 0) {
+          bulk_s2g(a.pe_img + (size_t)tile * kPeBytes, sPE, kPeBytes);
+          bulk_commit();
+        }
+        store_pending = true;
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(pe_ready);
+
+      // ---- trunk epilogues: bias + ReLU in place in TMEM, 32 columns at a time ----
+      for (int l = 0; ok && l < 8; l++) {
+        if (!mbar_wait(acc_full, acc_ph, abort_flag)) { ok = false; break; }
+        acc_ph ^= 1;
+        tc_fence_after();
+        const uint32_t half = (l & 1) * 256;
+        const float* bl = sBias + l * 256;
+        for (int c = chalf; c < 8; c += 2) {
+          uint32_t v[32];
+          tmem_ld32(lane_addr + half + c * 32, v);
+          tmem_wait_ld();
+          uint32_t bits = 0;
+#pragma unroll
+          for (int j = 0; j < 32; j++) {
+            float h = __uint_as_float(v[j]) + bl[c * 32 + j];
+            h = fmaxf(h, 0.f);
+            bits |= (h > 0.f ? 1u : 0u) << j;
+            v[j] = to_tf32(h);
+          }
+          tmem_st32(lane_addr + half + c * 32, v);
+          if (a.save) {
+            uint8_t* dst = a.h_img + ((size_t)l * a.tiles + tile) * kHBytes + (size_t)c * kPanelBytes + row * 128;
+#pragma unroll
+            for (int j4 = 0; j4 < 8; j4++)
+              *(uint4*)(dst + ((j4 ^ (row & 7)) << 4)) = make_uint4(v[4 * j4], v[4 * j4 + 1], v[4 * j4 + 2], v[4 * j4 + 3]);
+            a.mask[(((size_t)l * a.tiles + tile) * 8 + c) * 128 + row] = bits;
+          }
+          tmem_wait_st();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&a_ready[c]);
+        }
+      }
+      if (!ok) break;
+      // ---- heads ----
+      if (!mbar_wait(acc_full, acc_ph, abort_flag)) { ok = false; break; }
+      acc_ph ^= 1;
+      tc_fence_after();
+      if (chalf == 0) {
+        uint32_t v[16];
+        tmem_ld16(lane_addr + 0, v);
+        tmem_wait_ld();
+        float o[16];
+        const float* bh = sBias + 8 * 256;
+#pragma unroll
+        for (int j = 0; j < 16; j++) o[j] = __uint_as_float(v[j]) + bh[j];
+        if (a.save) {
+          float4* dst = (float4*)(a.heads_out + ((size_t)tile * kRows + row) * 16);
+#pragma unroll
+          for (int j = 0; j < 4; j++) dst[j] = make_float4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+        }
+        if (live) {
+          if (!a.is_6dof) {
+            a.d_xyz[3 * grow] = o[0]; a.d_xyz[3 * grow + 1] = o[1]; a.d_xyz[3 * grow + 2] = o[2];
+            if (a.d_rot) { *(float4*)(a.d_rot + 4 * grow) = make_float4(o[3], o[4], o[5], o[6]); }
+            if (a.d_scale) { a.d_scale[3 * grow] = o[7]; a.d_scale[3 * grow + 1] = o[8]; a.d_scale[3 * grow + 2] = o[9]; }
+          } else {
+            // utils/time_utils.py:114-121 + utils/rigid_utils.py:60-83 (exp_se3)
+            float w0 = o[0], w1 = o[1], w2 = o[2], v0 = o[3], v1 = o[4], v2 = o[5];
+            float theta = sqrtf(w0 * w0 + w1 * w1 + w2 * w2);
+            w0 = w0 / theta + 1e-5f; w1 = w1 / theta + 1e-5f; w2 = w2 / theta + 1e-5f;
+            v0 = v0 / theta + 1e-5f; v1 = v1 / theta + 1e-5f; v2 = v2 / theta + 1e-5f;
+            float sn, cs;
+            sincosf(theta, &sn, &cs);
+            float W[9] = {0.f, -w2, w1, w2, 0.f, -w0, -w1, w0, 0.f};
+            float W2[9];
+#pragma unroll
+            for (int i = 0; i < 3; i++)
+#pragma unroll
+              for (int j = 0; j < 3; j++)
+                W2[3 * i + j] = W[3 * i] * W[j] + W[3 * i + 1] * W[3 + j] + W[3 * i + 2] * W[6 + j];
+            float R[9], Pm[9];
+#pragma unroll
+            for (int i = 0; i < 9; i++) {
+              float id = (i == 0 || i == 4 || i == 8) ? 1.f : 0.f;
+              R[i] = id + sn * W[i] + (1.0f - cs) * W2[i];
+              Pm[i] = theta * id + (1.0f - cs) * W[i] + (theta - sn) * W2[i];
+            }
+            float p0 = Pm[0] * v0 + Pm[1] * v1 + Pm[2] * v2;
+            float p1 = Pm[3] * v0 + Pm[4] * v1 + Pm[5] * v2;
+            float p2 = Pm[6] * v0 + Pm[7] * v1 + Pm[8] * v2;
+            float4* out = (float4*)(a.d_xyz + 16 * grow);
+            out[0] = make_float4(R[0], R[1], R[2], p0);
+            out[1] = make_float4(R[3], R[4], R[5], p1);
+            out[2] = make_float4(R[6], R[7], R[8], p2);
+            out[3] = make_float4(0.f, 0.f, 0.f, 1.f);
+            if (a.d_rot) { *(float4*)(a.d_rot + 4 * grow) = make_float4(o[6], o[7], o[8], o[9]); }
+            if (a.d_scale) { a.d_scale[3 * grow] = o[10]; a.d_scale[3 * grow + 1] = o[11]; a.d_scale[3 * grow + 2] = o[12]; }
+          }
+        }
+      }
+      tc_fence_before();
+    }
+    if (store_pending && tid == 0) bulk_wait_all<0>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 9) tmem_dealloc(tmem_base, 512);
+}
+
+// ------------------------------------------------------------------------------------------------
+// small helper kernels
+// ------------------------------------------------------------------------------------------------
+
+// Time feature: blender -> timenet(PE_6(t)) = 13 -> 256 -> ReLU -> 30 (utils/time_utils.py:74-76,105);
+// otherwise PE_10(t) (21 values).  One CTA of 256 threads per distinct time value.
+__global__ void __launch_bounds__(256)
+tfeat_kernel(int64_t rows_t, const float* __restrict__ t, int64_t t_stride, int is_blender,
+             const float* __restrict__ w0, const float* __restrict__ b0, const float* __restrict__ w2,
+             const float* __restrict__ b2, float* __restrict__ tfeat, float* __restrict__ thidden) {
+  __shared__ float e[32];
+  __shared__ float hid[256];
+  int64_t r = blockIdx.x;
+  if (r >= rows_t) return;
+  float tv = t[r * t_stride];
+  int L = is_blender ? 6 : 10;
+  if (threadIdx.x < 32) {
+    int j = threadIdx.x;
+    float v = 0.f;
+    if (j == 0) v = tv;
+    else if (j < 1 + 2 * L) {
+      int f = (j - 1) >> 1;
+      float arg = tv * (float)(1 << f);
+      v = ((j - 1) & 1) ? cosf(arg) : sinf(arg);
+    }
+    e[j] = v;
+  }
+  __syncthreads();
+  if (!is_blender) {
+    if (threadIdx.x < 32) tfeat[r * 32 + threadIdx.x] = threadIdx.x < 21 ? e[threadIdx.x] : 0.f;
+    return;
+  }
+  {
+    int j = threadIdx.x;
+    float acc = b0[j];
+#pragma unroll
+    for (int k = 0; k < 13; k++) acc += w0[j * 13 + k] * e[k];
+    acc = fmaxf(acc, 0.f);
+    hid[j] = acc;
+    if (thidden) thidden[r * 256 + j] = acc;
+  }
+  __syncthreads();
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = warp; i < 32; i += 8) {
+    float acc = 0.f;
+    if (i < 30)
+      for (int k = lane; k < 256; k += 32) acc += w2[i * 256 + k] * hid[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) tfeat[r * 32 + i] = i < 30 ? acc + b2[i] : 0.f;
+  }
+}
+
+// Pack parameters into the streaming images (forward stages, biases, transposed backward stages).
+__global__ void __launch_bounds__(256)
+pack_weights_kernel(d3g_mlp_config cfg, d3g_mlp_params p, uint8_t* __restrict__ packed) {
+  const int pe_dim = cfg.is_blender ? 93 : 84;
+  int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int per_stage = 256 * 8;  // (row, 16-byte chunk)
+  const int n_fwd = kFwdStages * per_stage, n_bwd = kBwdStages * per_stage;
+  auto head_src = [&](int h, const float*& w, const float*& b, int& r) {
+    w = nullptr; b = nullptr; r = 0;
+    if (!cfg.is_6dof) {
+      if (h < 3) { w = p.warp_w; b = p.warp_b; r = h; }
+      else if (h < 7) { if (cfg.heads & 2) { w = p.rot_w; b = p.rot_b; r = h - 3; } }
+      else if (h < 10) { if (cfg.heads & 4) { w = p.scale_w; b = p.scale_b; r = h - 7; } }
+    } else {
+      if (h < 3) { w = p.branch_w_w; b = p.branch_w_b; r = h; }
+      else if (h < 6) { w = p.branch_v_w; b = p.branch_v_b; r = h - 3; }
+      else if (h < 10) { if (cfg.heads & 2) { w = p.rot_w; b = p.rot_b; r = h - 6; } }
+      else if (h < 13) { if (cfg.heads & 4) { w = p.scale_w; b = p.scale_b; r = h - 10; } }
+    }
+  };
+  if (gid < n_fwd) {
+    int st = gid / per_stage, rem = gid % per_stage, n = rem >> 3, j = rem & 7;
+    int layer, kp;
+    fwd_stage_info(st, layer, kp);
+    uint32_t vals[4] = {0, 0, 0, 0};
+    uint8_t* dst;
+    if (layer == 9) {
+      if (n >= 16) return;
+      // heads stage: 8 k-panels of 16 rows inside one 16 KB stage; this thread handles all 8 panels
+      const float* w; const float* b; int r;
+      head_src(n, w, b, r);
+      for (int kp2 = 0; kp2 < 8; kp2++) {
+#pragma unroll
+        for (int e = 0; e < 4; e++) vals[e] = w ? to_tf32(w[r * 256 + kp2 * 32 + j * 4 + e]) : 0u;
+        dst = packed + (size_t)st * kStageBytes + kp2 * 2048 + n * 128 + ((j ^ (n & 7)) << 4);
+        *(uint4*)dst = make_uint4(vals[0], vals[1], vals[2], vals[3]);
+      }
+      return;
+    }
+    const float* W; int ld, col0, ncols;
+    if (layer == 0) { W = p.linear_w[0]; ld = pe_dim; col0 = 0; ncols = pe_dim; }
+    else if (layer == 8) { W = p.linear_w[5]; ld = pe_dim + 256; col0 = 0; ncols = pe_dim; }
+    else if (layer == 5) { W = p.linear_w[5]; ld = pe_dim + 256; col0 = pe_dim; ncols = 256; }
+    else { W = p.linear_w[layer]; ld = 256; col0 = 0; ncols = 256; }
+#pragma unroll
+    for (int e = 0; e < 4; e++) {
+      int c = kp * 32 + j * 4 + e;
+      vals[e] = c < ncols ? to_tf32(W[(size_t)n * ld + col0 + c]) : 0u;
+    }
+    dst = packed + (size_t)st * kStageBytes + n * 128 + ((j ^ (n & 7)) << 4);
+    *(uint4*)dst = make_uint4(vals[0], vals[1], vals[2], vals[3]);
+    return;
+  }
+  gid -= n_fwd;
+  if (gid < n_bwd) {
+    // transposed images: row n = input feature, k = output feature (or head row)
+    int st = gid / per_stage, rem = gid % per_stage, n = rem >> 3, j = rem & 7;
+    int layer, kp;
+    bwd_stage_info(st, layer, kp);
+    uint32_t vals[4];
+#pragma unroll
+    for (int e = 0; e < 4; e++) {
+      int k = kp * 32 + j * 4 + e;
+      float v = 0.f;
+      if (layer == 9) {
+        if (k < 16) {
+          const float* w; const float* b; int r;
+          head_src(k, w, b, r);
+          if (w) v = w[r * 256 + n];
+        }
+      } else if (layer == 5) {
+        v = p.linear_w[5][(size_t)k * (pe_dim + 256) + pe_dim + n];
+      } else {
+        v = p.linear_w[layer][(size_t)k * 256 + n];
+      }
+      vals[e] = to_tf32(v);
+    }
+    uint8_t* dst = packed + kBwdOff + (size_t)st * kStageBytes + n * 128 + ((j ^ (n & 7)) << 4);
+    *(uint4*)dst = make_uint4(vals[0], vals[1], vals[2], vals[3]);
+    return;
+  }
+  gid -= n_bwd;
+  if (gid < kBiasFloats) {
+    float v = 0.f;
+    if (gid < 8 * 256) v = p.linear_b[gid >> 8][gid & 255];
+    else {
+      const float* w; const float* b; int r;
+      head_src(gid - 8 * 256, w, b, r);
+      if (b) v = b[r];
+    }
+    ((float*)(packed + kBiasOff))[gid] = v;
+  }
+}
+
+int check_cfg(const d3g_mlp_config* cfg) {
+  if (!cfg) return set_err(D3G_ERR_INVALID, "cfg is NULL");
+  if (cfg->D != 8 || cfg->W != 256 || cfg->multires != 10)
+    return set_err(D3G_ERR_UNSUPPORTED, "only D=8, W=256, multires=10 is implemented (got D=%d W=%d multires=%d)",
+                   cfg->D, cfg->W, cfg->multires);
+  if (!(cfg->heads & 1)) return set_err(D3G_ERR_INVALID, "heads bit0 (warp) must be set");
+  return 0;
+}
+
+static int g_num_sms = 0;
+int num_sms() {
+  if (!g_num_sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+  }
+  return g_num_sms;
+}
+
+}  // namespace d3g
+
+using namespace d3g;
+
+extern "C" {
+
+int d3g_mlp_packed_bytes(const d3g_mlp_config* cfg, size_t* bytes) {
+  if (int e = check_cfg(cfg)) return e;
+  if (!bytes) return set_err(D3G_ERR_INVALID, "bytes is NULL");
+  *bytes = kPackedBytes;
+  return 0;
+}
+
+int d3g_mlp_workspace_bytes(const d3g_mlp_config* cfg, int64_t rows, int32_t save, size_t* bytes) {
+  if (int e = check_cfg(cfg)) return e;
+  if (!bytes || rows < 0) return set_err(D3G_ERR_INVALID, "bad arguments");
+  *bytes = mlp_ws_view(nullptr, rows, save != 0).total;
+  return 0;
+}
+
+int d3g_mlp_pack_weights(const d3g_mlp_config* cfg, const d3g_mlp_params* p, void* packed, void* stream_) {
+  if (int e = check_cfg(cfg)) return e;
+  if (!p || !packed) return set_err(D3G_ERR_INVALID, "NULL argument");
+  for (int l = 0; l < 8; l++)
+    if (!p->linear_w[l] || !p->linear_b[l]) return set_err(D3G_ERR_INVALID, "linear.%d parameters missing", l);
+  if (cfg->is_6dof ? (!p->branch_w_w || !p->branch_v_w) : !p->warp_w)
+    return set_err(D3G_ERR_INVALID, "warp head parameters missing");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  int total = (kFwdStages + kBwdStages) * 256 * 8 + kBiasFloats;
+  pack_weights_kernel<<<(total + 255) / 256, 256, 0, stream>>>(*cfg, *p, (uint8_t*)packed);
+  D3G_LAUNCH_CHECK(0, stream);
+  return 0;
+}
+
+int d3g_mlp_forward(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp_params* p, int64_t rows,
+                    const float* xyz, const float* t, int64_t t_stride, void* workspace, int32_t save,
+                    float* d_xyz, float* d_rot, float* d_scale, void* stream_) {
+  if (int e = check_cfg(cfg)) return e;
+  if (!packed || !p || !workspace) return set_err(D3G_ERR_INVALID, "NULL argument");
+  if (rows < 0 || (rows > 0 && (!xyz || !t || !d_xyz))) return set_err(D3G_ERR_INVALID, "NULL tensor");
+  if (cfg->is_blender && (!p->timenet0_w || !p->timenet0_b || !p->timenet2_w || !p->timenet2_b))
+    return set_err(D3G_ERR_INVALID, "timenet parameters missing");
+  if (rows > ((int64_t)1 << 31) - 256) return set_err(D3G_ERR_CAPACITY, "too many rows");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  MlpWs ws = mlp_ws_view(workspace, rows, save != 0);
+  D3G_CUDA_TRY(cudaMemsetAsync(ws.status, 0, 4, stream));
+  if (rows == 0) return 0;
+  int64_t rows_t = t_stride == 0 ? 1 : rows;
+  tfeat_kernel<<<(unsigned)rows_t, 256, 0, stream>>>(rows_t, t, t_stride, cfg->is_blender, p->timenet0_w,
+                                                     p->timenet0_b, p->timenet2_w, p->timenet2_b, ws.tfeat,
+                                                     save ? ws.thidden : nullptr);
+  D3G_LAUNCH_CHECK(0, stream);
+  MlpFwdArgs a;
+  a.wfwd = (const uint8_t*)packed;
+  a.bias = (const float*)((const uint8_t*)packed + kBiasOff);
+  a.xyz = xyz; a.rows = rows; a.tiles = (int)((rows + kRows - 1) / kRows);
+  a.tfeat = ws.tfeat; a.tfeat_stride = t_stride == 0 ? 0 : 32;
+  a.pe_dim = cfg->is_blender ? 93 : 84; a.t_dim = cfg->is_blender ? 30 : 21;
+  a.is_6dof = cfg->is_6dof; a.heads = cfg->heads; a.save = save != 0;
+  a.pe_img = ws.pe_img; a.h_img = ws.h_img; a.mask = ws.mask; a.heads_out = ws.heads_out;
+  a.d_xyz = d_xyz; a.d_rot = (cfg->heads & 2) ? d_rot : nullptr; a.d_scale = (cfg->heads & 4) ? d_scale : nullptr;
+  a.abort_flag = ws.status;
+  size_t smem = FwdSmem::total + 1024;
+  D3G_CUDA_TRY(cudaFuncSetAttribute(mlp_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int grid = a.tiles < num_sms() ? a.tiles : num_sms();
+  mlp_fwd_kernel<<<grid, kFwdThreads, smem, stream>>>(a);
+  D3G_LAUNCH_CHECK(0, stream);
+  return 0;
+}
+
+int d3g_mlp_read_status(const void* workspace, int32_t* status_host, void* stream_) {
+  if (!workspace || !status_host) return set_err(D3G_ERR_INVALID, "NULL argument");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  D3G_CUDA_TRY(cudaMemcpyAsync(status_host, workspace, 4, cudaMemcpyDeviceToHost, stream));
+  D3G_CUDA_TRY(cudaStreamSynchronize(stream));
+  return 0;
+}
+
+}  // extern "C"

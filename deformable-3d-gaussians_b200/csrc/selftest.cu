@@ -1,0 +1,140 @@
+// tcgen05 self-test: one CTA computes D[128,N] = A[128,K] * B[N,K]^T through exactly the operand
+// conventions the MLP kernels use (panelised SWIZZLE_128B images, kind::tf32, accumulators in TMEM).
+// Called from tests/ through d3g_selftest_umma; it exists so that a wrong descriptor bit shows up as
+// a small, localised GEMM failure instead of a wrong MLP.
+#include "common.cuh"
+#include "umma.cuh"
+
+namespace d3g {
+
+// mode 0: A,B K-major in smem (A given [128,K], B given [N,K])
+// mode 1: A in TMEM (written with tcgen05.st), B K-major in smem
+// mode 2: A,B MN-major in smem (A given [K,128], B given [K,N])
+__global__ void __launch_bounds__(128, 1)
+selftest_umma_kernel(int mode, int N, int K, const float* __restrict__ A, const float* __restrict__ B,
+                     float* __restrict__ D, int* abort_flag) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_base_s;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const uint32_t kpanels = (K + 31) / 32;
+  uint8_t* sA = smem;
+  uint32_t a_panel_stride, b_panel_stride, a_bytes;
+  if (mode == 2) {
+    a_panel_stride = (uint32_t)K * 128u;  // K rows per panel, 4 panels (M=128)
+    a_bytes = 4u * a_panel_stride;
+    b_panel_stride = (uint32_t)K * 128u;  // N/32 panels
+  } else {
+    a_panel_stride = 128u * 128u;
+    a_bytes = kpanels * a_panel_stride;
+    b_panel_stride = (uint32_t)N * 128u;
+  }
+  uint8_t* sB = sA + ((a_bytes + 1023u) & ~1023u);
+
+  if (warp == 0) tmem_alloc(&tmem_base_s, 512);
+  if (tid == 0) {
+    mbar_init(&bar, 1);
+    fence_barrier_init();
+  }
+  // stage operands
+  if (mode == 2) {
+    for (int i = tid; i < K * 128; i += 128) {
+      int k = i / 128, m = i % 128;
+      *(uint32_t*)(sA + img_off(k, m, a_panel_stride)) = to_tf32(A[(size_t)k * 128 + m]);
+    }
+    for (int i = tid; i < K * N; i += 128) {
+      int k = i / N, n = i % N;
+      *(uint32_t*)(sB + img_off(k, n, b_panel_stride)) = to_tf32(B[(size_t)k * N + n]);
+    }
+  } else {
+    if (mode == 0)
+      for (int i = tid; i < 128 * K; i += 128) {
+        int r = i / K, c = i % K;
+        *(uint32_t*)(sA + img_off(r, c, a_panel_stride)) = to_tf32(A[(size_t)r * K + c]);
+      }
+    for (int i = tid; i < N * K; i += 128) {
+      int r = i / K, c = i % K;
+      *(uint32_t*)(sB + img_off(r, c, b_panel_stride)) = to_tf32(B[(size_t)r * K + c]);
+    }
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+  const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+  const uint32_t a_col0 = 256;
+  if (mode == 1) {
+    // every thread owns one row of A; K is a multiple of 32 in this mode
+    for (int c0 = 0; c0 < K; c0 += 32) {
+      uint32_t v[32];
+#pragma unroll
+      for (int j = 0; j < 32; j++) v[j] = to_tf32(A[(size_t)tid * K + c0 + j]);
+      tmem_st32(lane_addr + a_col0 + c0, v);
+    }
+    tmem_wait_st();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+  }
+  if (tid == 0) {
+    const uint32_t a_mn = mode == 2, b_mn = mode == 2;
+    const uint32_t idesc = make_idesc_tf32(128, N, a_mn, b_mn);
+    for (int k8 = 0; k8 < K / 8; k8++) {
+      uint64_t bdesc, adesc = 0;
+      if (mode == 2) {
+        adesc = make_smem_desc(smem_u32(sA) + k8 * 1024, a_panel_stride, 1024);
+        bdesc = make_smem_desc(smem_u32(sB) + k8 * 1024, b_panel_stride, 1024);
+      } else {
+        adesc = make_smem_desc(smem_u32(sA) + (k8 / 4) * a_panel_stride + (k8 % 4) * 32, 16, 1024);
+        bdesc = make_smem_desc(smem_u32(sB) + (k8 / 4) * b_panel_stride + (k8 % 4) * 32, 16, 1024);
+      }
+      if (mode == 1) umma_tf32_ts(tmem_base, tmem_base + a_col0 + k8 * 8, bdesc, idesc, k8 > 0);
+      else umma_tf32_ss(tmem_base, adesc, bdesc, idesc, k8 > 0);
+    }
+    umma_commit(&bar);
+  }
+  bool ok = mbar_wait(&bar, 0, abort_flag);
+  tc_fence_after();
+  if (ok) {
+    for (int c0 = 0; c0 < N; c0 += 32) {
+      uint32_t v[32];
+      tmem_ld32(lane_addr + c0, v);
+      tmem_wait_ld();
+#pragma unroll
+      for (int j = 0; j < 32; j++)
+        if (c0 + j < N) D[(size_t)tid * N + c0 + j] = __uint_as_float(v[j]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, 512);
+}
+
+}  // namespace d3g
+
+using namespace d3g;
+
+extern "C" int d3g_selftest_umma(int32_t mode, int32_t N, int32_t K, const float* A, const float* B, float* D,
+                                 void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (mode < 0 || mode > 2) return set_err(D3G_ERR_INVALID, "mode must be 0..2");
+  if (N < 32 || N > 256 || N % 32 || K < 8 || K > 64 || K % 8 || (mode == 1 && K % 32))
+    return set_err(D3G_ERR_INVALID, "unsupported self-test shape N=%d K=%d", N, K);
+  int* flag = nullptr;
+  D3G_CUDA_TRY(cudaMalloc(&flag, sizeof(int)));
+  D3G_CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(int), stream));
+  size_t smem = 1024 + 4 * 128 * 128 + 8 * 64 * 128 * 4 + 2048;
+  smem = 1024 + 65536 + 65536 + 2048;
+  D3G_CUDA_TRY(cudaFuncSetAttribute(selftest_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  selftest_umma_kernel<<<1, 128, smem, stream>>>(mode, N, K, A, B, D, flag);
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+  int h = 0;
+  if (e == cudaSuccess) e = cudaMemcpy(&h, flag, sizeof(int), cudaMemcpyDeviceToHost);
+  cudaFree(flag);
+  if (e != cudaSuccess) return set_err(D3G_ERR_CUDA, "self-test failed: %s", cudaGetErrorString(e));
+  if (h) return set_err(D3G_ERR_CUDA, "self-test: mbarrier wait timed out (protocol error)");
+  return 0;
+}

@@ -1,0 +1,327 @@
+"""Drop-in for the reference's deformation networks and their wrappers.
+
+`DeformNetwork` / `DeformNetworkBaseline` mirror utils/time_utils.py:56-201 (same constructor
+arguments, same parameter names / shapes / construction order, so `state_dict()` files and seeded
+initialisation are interchangeable); `DeformModel` / `DeformModelBaseline` mirror
+scene/deform_model.py:253-337 (`.deform`, `.optimizer`, `.spatial_lr_scale`, `.step`,
+`.train_setting`, `.save_weights`, `.load_weights`, `.update_learning_rate`).
+
+forward() does no torch math: positional encoding, the 8x256 trunk, the heads and the se(3) map run in
+the fused tcgen05 kernels of libd3g.so through the C ABI (d3g_mlp_forward / d3g_mlp_backward).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+HEAD_WARP, HEAD_ROT, HEAD_SCALE = 1, 2, 4
+
+
+def _param_list(net):
+    """(name, tensor) in the fixed order of the C structs d3g_mlp_params / d3g_mlp_grads."""
+    out = []
+    if net.is_blender:
+        out += [("timenet0_w", net.timenet[0].weight), ("timenet0_b", net.timenet[0].bias),
+                ("timenet2_w", net.timenet[2].weight), ("timenet2_b", net.timenet[2].bias)]
+    for i in range(8):
+        out += [("linear_w%d" % i, net.linear[i].weight), ("linear_b%d" % i, net.linear[i].bias)]
+    if net.is_6dof:
+        out += [("branch_w_w", net.branch_w.weight), ("branch_w_b", net.branch_w.bias),
+                ("branch_v_w", net.branch_v.weight), ("branch_v_b", net.branch_v.bias)]
+    else:
+        out += [("warp_w", net.gaussian_warp.weight), ("warp_b", net.gaussian_warp.bias)]
+    out += [("rot_w", net.gaussian_rotation.weight), ("rot_b", net.gaussian_rotation.bias),
+            ("scale_w", net.gaussian_scaling.weight), ("scale_b", net.gaussian_scaling.bias)]
+    return out
+
+
+def _fill_ptr_struct(struct, named):
+    for name, t in named:
+        ptr = 0 if t is None else t.data_ptr()
+        if name.startswith("linear_w"):
+            struct.linear_w[int(name[8:])] = ptr
+        elif name.startswith("linear_b"):
+            struct.linear_b[int(name[8:])] = ptr
+        else:
+            setattr(struct, name, ptr)
+    return struct
+
+
+class _FusedDeform(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, net, xyz, t, *params):
+        lib = _lib.load()
+        dev = xyz.device
+        if dev.type != "cuda":
+            raise RuntimeError("DeformNetwork: tensors must live on a CUDA device (there is no CPU path)")
+        xyz_c = xyz.detach().contiguous().float()
+        rows = int(xyz_c.shape[0])
+        t2 = t.detach()
+        if t2.dim() == 2:
+            t2 = t2[:, 0]
+        if t2.dtype != torch.float32:
+            t2 = t2.float()
+        if t2.numel() == 1:
+            t_stride = 0
+        else:
+            t_stride = int(t2.stride(0))
+        cfg = net._cfg()
+        packed = net._packed(dev)
+        need_grad = torch.is_grad_enabled() and (any(p.requires_grad for p in params) or xyz.requires_grad)
+        wsb = C.c_size_t()
+        _lib.check(lib.d3g_mlp_workspace_bytes(C.byref(cfg), rows, int(need_grad), C.byref(wsb)))
+        ws = torch.empty(wsb.value, dtype=torch.uint8, device=dev)
+        pstruct = _fill_ptr_struct(_lib.MlpParams(), _param_list(net))
+        d_xyz = torch.empty((rows, 4, 4) if net.is_6dof else (rows, 3), dtype=torch.float32, device=dev)
+        d_rot = torch.empty(rows, 4, dtype=torch.float32, device=dev) if net._heads & HEAD_ROT else None
+        d_scale = torch.empty(rows, 3, dtype=torch.float32, device=dev) if net._heads & HEAD_SCALE else None
+        stream = torch.cuda.current_stream().cuda_stream
+        _lib.check(lib.d3g_mlp_forward(C.byref(cfg), _lib.ptr(packed), C.byref(pstruct), C.c_int64(rows),
+                                       _lib.ptr(xyz_c), _lib.ptr(t2), C.c_int64(t_stride), _lib.ptr(ws),
+                                       int(need_grad), _lib.ptr(d_xyz), _lib.ptr(d_rot), _lib.ptr(d_scale),
+                                       C.c_void_p(stream)))
+        if net.debug:
+            net._check_status(ws)
+        ctx.net, ctx.ws, ctx.rows, ctx.t_stride = net, ws, rows, t_stride
+        ctx.xyz_requires_grad = xyz.requires_grad
+        ctx.save_for_backward(xyz_c, t2)
+        ctx.set_materialize_grads(False)
+        outs = [d_xyz]
+        if d_rot is not None:
+            outs.append(d_rot)
+        if d_scale is not None:
+            outs.append(d_scale)
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, *gouts):
+        lib = _lib.load()
+        net = ctx.net
+        xyz_c, t2 = ctx.saved_tensors
+        dev = xyz_c.device
+        rows = ctx.rows
+        it = iter(gouts)
+        g_xyz = next(it)
+        g_rot = next(it) if net._heads & HEAD_ROT else None
+        g_scale = next(it) if net._heads & HEAD_SCALE else None
+        f = lambda g: None if g is None else g.contiguous().float()
+        g_xyz, g_rot, g_scale = f(g_xyz), f(g_rot), f(g_scale)
+        named = _param_list(net)
+        grads = [torch.zeros_like(p, dtype=torch.float32) for _, p in named]
+        gstruct = _fill_ptr_struct(_lib.MlpGrads(), [(n, g) for (n, _), g in zip(named, grads)])
+        pstruct = _fill_ptr_struct(_lib.MlpParams(), named)
+        cfg = net._cfg()
+        packed = net._packed(dev)
+        dxyz_in = torch.empty(rows, 3, dtype=torch.float32, device=dev) if ctx.xyz_requires_grad else None
+        stream = torch.cuda.current_stream().cuda_stream
+        _lib.check(lib.d3g_mlp_backward(C.byref(cfg), _lib.ptr(packed), C.byref(pstruct), C.c_int64(rows),
+                                        _lib.ptr(xyz_c), _lib.ptr(t2), C.c_int64(ctx.t_stride), _lib.ptr(ctx.ws),
+                                        _lib.ptr(g_xyz), _lib.ptr(g_rot), _lib.ptr(g_scale), C.byref(gstruct),
+                                        _lib.ptr(dxyz_in), C.c_void_p(0), C.c_void_p(stream)))
+        if net.debug:
+            net._check_status(ctx.ws)
+        ctx.ws = None
+        # heads the network never evaluates get no gradient at all (like autograd in the reference), so
+        # Adam's weight decay does not touch them
+        unused = set()
+        if not net._heads & HEAD_ROT:
+            unused |= {"rot_w", "rot_b"}
+        if not net._heads & HEAD_SCALE:
+            unused |= {"scale_w", "scale_b"}
+        out = tuple(None if n in unused else g for (n, _), g in zip(named, grads))
+        return (None, dxyz_in, None) + out
+
+
+class _DeformBase(nn.Module):
+    """Shared constructor: identical module tree to utils/time_utils.py:57-100 / :130-174."""
+
+    def __init__(self, D=8, W=256, input_ch=3, output_ch=59, multires=10, is_blender=False, is_6dof=False):
+        super().__init__()
+        self.D, self.W = D, W
+        self.output_ch = output_ch
+        self.multires = multires
+        self.t_multires = 6 if is_blender else 10
+        self.skips = [D // 2]
+        time_input_ch = 1 + 2 * self.t_multires
+        xyz_input_ch = 3 + 6 * multires
+        self.input_ch = xyz_input_ch + time_input_ch
+        if is_blender:
+            self.time_out = 30
+            self.timenet = nn.Sequential(nn.Linear(time_input_ch, 256), nn.ReLU(inplace=True),
+                                         nn.Linear(256, self.time_out))
+            first = xyz_input_ch + self.time_out
+        else:
+            first = self.input_ch
+        self.linear = nn.ModuleList(
+            [nn.Linear(first, W)] + [nn.Linear(W, W) if i not in self.skips else nn.Linear(W + first, W)
+                                     for i in range(D - 1)])
+        self.is_blender = is_blender
+        self.is_6dof = is_6dof
+        if is_6dof:
+            self.branch_w = nn.Linear(W, 3)
+            self.branch_v = nn.Linear(W, 3)
+        else:
+            self.gaussian_warp = nn.Linear(W, 3)
+        self.gaussian_rotation = nn.Linear(W, 4)
+        self.gaussian_scaling = nn.Linear(W, 3)
+        self.debug = bool(int(os.environ.get("D3G_DEBUG", "0")))
+        self._pack_cache = None
+
+    # -- C-ABI plumbing --------------------------------------------------------------------------
+    def _cfg(self):
+        c = _lib.MlpConfig()
+        c.is_blender, c.is_6dof, c.heads = int(self.is_blender), int(self.is_6dof), int(self._heads)
+        c.D, c.W, c.multires = int(self.D), int(self.W), int(self.multires)
+        return c
+
+    def _packed(self, dev):
+        """Packed weight images, rebuilt only when a parameter changed (tensor version counters)."""
+        lib = _lib.load()
+        named = _param_list(self)
+        key = tuple((p.data_ptr(), p._version) for _, p in named) + (str(dev),)
+        if self._pack_cache is not None and self._pack_cache[0] == key:
+            return self._pack_cache[1]
+        cfg = self._cfg()
+        nb = C.c_size_t()
+        _lib.check(lib.d3g_mlp_packed_bytes(C.byref(cfg), C.byref(nb)))
+        buf = self._pack_cache[1] if self._pack_cache is not None and self._pack_cache[1].device == dev \
+            else torch.empty(nb.value, dtype=torch.uint8, device=dev)
+        for _, p in named:
+            if p.device != dev or p.dtype != torch.float32 or not p.is_contiguous():
+                raise RuntimeError("DeformNetwork parameters must be contiguous fp32 tensors on %s" % dev)
+        pstruct = _fill_ptr_struct(_lib.MlpParams(), named)
+        _lib.check(lib.d3g_mlp_pack_weights(C.byref(cfg), C.byref(pstruct), _lib.ptr(buf),
+                                            C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        self._pack_cache = (key, buf)
+        return buf
+
+    def _check_status(self, ws):
+        lib = _lib.load()
+        st = C.c_int32(0)
+        _lib.check(lib.d3g_mlp_read_status(_lib.ptr(ws), C.byref(st),
+                                           C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        if st.value != 0:
+            raise _lib.D3GError("fused MLP kernel reported an internal pipeline timeout (status %d)" % st.value)
+
+    def _run(self, x, t):
+        params = [p for _, p in _param_list(self)]
+        return _FusedDeform.apply(self, x, t, *params)
+
+
+class DeformNetworkBaseline(_DeformBase):
+    """utils/time_utils.py:56-127: returns (d_xyz, rotation, scaling)."""
+    _heads = HEAD_WARP | HEAD_ROT | HEAD_SCALE
+
+    def forward(self, x, t):
+        d_xyz, rotation, scaling = self._run(x, t)
+        return d_xyz, rotation, scaling
+
+
+class DeformNetwork(_DeformBase):
+    """utils/time_utils.py:129-201: same trunk, returns (d_xyz, 0, 0)."""
+    _heads = HEAD_WARP
+
+    def forward(self, x, t):
+        (d_xyz,) = self._run(x, t)
+        return d_xyz, 0, 0
+
+
+def get_expon_lr_func(lr_init, lr_final, lr_delay_steps=0, lr_delay_mult=1.0, max_steps=1000000):
+    """utils/general_utils.py:78-109 (log-linear interpolation with optional warm-up)."""
+
+    def helper(step):
+        if step < 0 or (lr_init == 0.0 and lr_final == 0.0):
+            return 0.0
+        if lr_delay_steps > 0:
+            delay_rate = lr_delay_mult + (1 - lr_delay_mult) * np.sin(0.5 * np.pi * np.clip(step / lr_delay_steps, 0, 1))
+        else:
+            delay_rate = 1.0
+        tt = np.clip(step / max_steps, 0, 1)
+        log_lerp = np.exp(np.log(lr_init) * (1 - tt) + np.log(lr_final) * tt)
+        return delay_rate * log_lerp
+
+    return helper
+
+
+def _search_max_iteration(folder):
+    return max(int(f.split("_")[-1]) for f in os.listdir(folder))
+
+
+class _DeformModelBase:
+    def save_weights(self, model_path, iteration):
+        out = os.path.join(model_path, "deform/iteration_{}".format(iteration))
+        os.makedirs(out, exist_ok=True)
+        torch.save(self.deform.state_dict(), os.path.join(out, "deform.pth"))
+
+    def load_weights(self, model_path, iteration=-1):
+        it = _search_max_iteration(os.path.join(model_path, "deform")) if iteration == -1 else iteration
+        path = os.path.join(model_path, "deform/iteration_{}/deform.pth".format(it))
+        self.deform.load_state_dict(torch.load(path))
+
+    def update_learning_rate(self, iteration):
+        for group in self.optimizer.param_groups:
+            if group["name"] == "deform":
+                lr = self.deform_scheduler_args(iteration)
+                group["lr"] = lr
+                return lr
+
+
+class DeformModel(_DeformModelBase):
+    """scene/deform_model.py:253-308."""
+
+    def __init__(self, is_blender=False, is_6dof=False, D=8, W=256, input_ch=3, output_ch=59, multires=10,
+                 scale_lr=False):
+        self.deform = DeformNetwork(is_blender=is_blender, is_6dof=is_6dof, D=D, W=W, input_ch=input_ch,
+                                    output_ch=output_ch, multires=multires).cuda()
+        self.optimizer = None
+        self.spatial_lr_scale = 5
+        self.scale_lr = scale_lr
+
+    def step(self, xyz, time_emb):
+        d_xyz_list, d_rotation_list, d_scaling_list = [], [], []
+        for i in range(time_emb.shape[1]):
+            d_xyz, d_rotation, d_scaling = self.deform(xyz, time_emb[:, i].unsqueeze(1))
+            d_xyz_list.append(d_xyz)
+            d_rotation_list.append(d_rotation)
+            d_scaling_list.append(d_scaling)
+        return torch.stack(d_xyz_list, dim=0), d_rotation_list, d_scaling_list
+
+    def train_setting(self, training_args):
+        l = [{"params": list(self.deform.parameters()),
+              "lr": training_args.position_lr_init * self.spatial_lr_scale, "name": "deform"}]
+        self.optimizer = torch.optim.Adam(l, lr=0.0, eps=1e-15, weight_decay=training_args.weight_decay)
+        if self.scale_lr:
+            lr_init = training_args.position_lr_init * self.spatial_lr_scale * training_args.num_cams_per_iter
+            lr_final = training_args.position_lr_final * training_args.num_cams_per_iter
+        else:
+            lr_init = training_args.position_lr_init * self.spatial_lr_scale
+            lr_final = training_args.position_lr_final
+        self.deform_scheduler_args = get_expon_lr_func(lr_init=lr_init, lr_final=lr_final,
+                                                       lr_delay_mult=training_args.position_lr_delay_mult,
+                                                       max_steps=training_args.position_lr_max_steps)
+
+
+class DeformModelBaseline(_DeformModelBase):
+    """scene/deform_model.py:317-356."""
+
+    def __init__(self, is_blender=False, is_6dof=False, D=8, W=256, input_ch=3, output_ch=59, multires=10):
+        self.deform = DeformNetworkBaseline(is_blender=is_blender, is_6dof=is_6dof, D=D, W=W, input_ch=input_ch,
+                                            output_ch=output_ch, multires=multires).cuda()
+        self.optimizer = None
+        self.spatial_lr_scale = 5
+
+    def step(self, xyz, time_emb):
+        return self.deform(xyz, time_emb)
+
+    def train_setting(self, training_args):
+        l = [{"params": list(self.deform.parameters()),
+              "lr": training_args.position_lr_init * self.spatial_lr_scale, "name": "deform"}]
+        self.optimizer = torch.optim.Adam(l, lr=0.0, eps=1e-15)
+        self.deform_scheduler_args = get_expon_lr_func(
+            lr_init=training_args.position_lr_init * self.spatial_lr_scale,
+            lr_final=training_args.position_lr_final, lr_delay_mult=training_args.position_lr_delay_mult,
+            max_steps=training_args.deform_lr_max_steps)

@@ -1,0 +1,216 @@
+"""Drop-in for the reference's `diff_gaussian_rasterization` Python module.
+
+Same names, argument meaning and error behaviour as the module imported at
+gaussian_renderer/__init__.py:14 and used at :53-68 / :115-124: `GaussianRasterizationSettings` is a
+NamedTuple with the twelve fields the reference passes by keyword, `GaussianRasterizer(raster_settings)`
+is an nn.Module whose call returns `(color[3,H,W], radii[N] int32, depth[1,H,W])`, and gradients flow
+to means3D, means2D, means2D_densify, shs / colors_precomp, opacities, scales, rotations /
+cov3D_precomp.  All compute goes through the C ABI of libd3g.so (include/d3g.h); this file only
+forwards data pointers and the current CUDA stream.
+"""
+import ctypes as C
+from typing import NamedTuple
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+
+
+# Semantics of means2D_densify.grad (DESIGN.md "open semantic #1"); 2 = sum of |per-pixel term|.
+DENSIFY_MODE = 2
+
+# Optional sync-free operation: when set to a callable (N, H, W) -> pair capacity, forward sizes the
+# binning workspace from it instead of reading the pair count back from the device.
+PAIR_CAPACITY_POLICY = None
+
+_pinned = {}
+
+
+def _pinned_u32(device):
+    key = (device.index if device.index is not None else torch.cuda.current_device())
+    if key not in _pinned:
+        _pinned[key] = torch.zeros(4, dtype=torch.int32).pin_memory()
+    return _pinned[key]
+
+
+def _f32c(t):
+    if t is None:
+        return None
+    if t.dtype != torch.float32 or not t.is_contiguous():
+        t = t.contiguous().float()
+    return t
+
+
+def _settings_struct(rs, keep):
+    """Build the C struct; `keep` collects the tensors whose pointers it holds."""
+    bg, view, proj, campos = (_f32c(rs.bg), _f32c(rs.viewmatrix), _f32c(rs.projmatrix), _f32c(rs.campos))
+    keep.extend([bg, view, proj, campos])
+    s = _lib.RasterSettings()
+    s.image_height, s.image_width = int(rs.image_height), int(rs.image_width)
+    s.tanfovx, s.tanfovy = float(rs.tanfovx), float(rs.tanfovy)
+    s.bg, s.viewmatrix, s.projmatrix, s.campos = bg.data_ptr(), view.data_ptr(), proj.data_ptr(), campos.data_ptr()
+    s.scale_modifier = float(rs.scale_modifier)
+    s.sh_degree = int(rs.sh_degree)
+    s.prefiltered, s.debug = int(bool(rs.prefiltered)), int(bool(rs.debug))
+    s.densify_mode = DENSIFY_MODE
+    return s
+
+
+def _sizes(lib, N, H, W):
+    gb, ib = C.c_size_t(), C.c_size_t()
+    _lib.check(lib.d3g_raster_geom_bytes(N, C.byref(gb)))
+    _lib.check(lib.d3g_raster_img_bytes(H, W, C.byref(ib)))
+    return gb.value, ib.value
+
+
+class RasterState:
+    """Opaque forward state (geometry / binning / image workspaces) kept for backward and for parity
+    inspection through d3g_raster_read_state."""
+
+    def __init__(self, N, H, W, cap, geom, binb, img, R):
+        self.N, self.H, self.W, self.cap, self.geom, self.bin, self.img, self.R = N, H, W, cap, geom, binb, img, R
+
+    def read(self, which, dtype, count):
+        lib = _lib.load()
+        out = torch.empty(count, dtype=dtype)
+        stream = torch.cuda.current_stream().cuda_stream
+        _lib.check(lib.d3g_raster_read_state(which, self.N, self.H, self.W, C.c_uint64(self.cap),
+                                             _lib.ptr(self.geom), _lib.ptr(self.bin), _lib.ptr(self.img),
+                                             C.c_void_p(out.data_ptr()), C.c_size_t(out.numel() * out.element_size()),
+                                             C.c_void_p(stream)))
+        return out
+
+
+def rasterize_forward(rs, means3D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp):
+    """Forward through the C ABI. Returns (color, radii, depth, RasterState)."""
+    lib = _lib.load()
+    dev = means3D.device
+    if dev.type != "cuda":
+        raise RuntimeError("GaussianRasterizer: tensors must live on a CUDA device (there is no CPU path)")
+    keep = []
+    s = _settings_struct(rs, keep)
+    N = int(means3D.shape[0])
+    H, W = s.image_height, s.image_width
+    M = int(shs.shape[1]) if shs is not None else 0
+    stream = torch.cuda.current_stream().cuda_stream
+    gb, ib = _sizes(lib, N, H, W)
+    geom = torch.empty(gb, dtype=torch.uint8, device=dev)
+    img = torch.empty(ib, dtype=torch.uint8, device=dev)
+    radii = torch.empty(N, dtype=torch.int32, device=dev)
+    color = torch.empty(3, H, W, dtype=torch.float32, device=dev)
+    depth = torch.empty(1, H, W, dtype=torch.float32, device=dev)
+    policy = PAIR_CAPACITY_POLICY
+    host = None if policy is not None else _pinned_u32(dev)
+    _lib.check(lib.d3g_raster_preprocess(C.byref(s), N, _lib.ptr(means3D), _lib.ptr(shs), M,
+                                         _lib.ptr(colors_precomp), _lib.ptr(opacities), _lib.ptr(scales),
+                                         _lib.ptr(rotations), _lib.ptr(cov3D_precomp), _lib.ptr(geom),
+                                         _lib.ptr(radii), C.c_void_p(0 if host is None else host.data_ptr()),
+                                         C.c_void_p(stream)))
+    if policy is None:
+        torch.cuda.current_stream().synchronize()
+        R = int(host[0].item()) & 0xFFFFFFFF
+        cap = R
+    else:
+        R = None
+        cap = int(policy(N, H, W))
+    bb = C.c_size_t()
+    _lib.check(lib.d3g_raster_bin_bytes(C.c_uint64(cap), C.byref(bb)))
+    binb = torch.empty(bb.value, dtype=torch.uint8, device=dev)
+    _lib.check(lib.d3g_raster_render(C.byref(s), N, C.c_uint64(cap), _lib.ptr(geom), _lib.ptr(binb),
+                                     _lib.ptr(img), _lib.ptr(radii), _lib.ptr(color), _lib.ptr(depth),
+                                     C.c_void_p(stream)))
+    return color, radii, depth, RasterState(N, H, W, cap, geom, binb, img, R)
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, means2D_densify, sh, colors_precomp, opacities, scales, rotations,
+                cov3Ds_precomp, raster_settings):
+        means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp = map(
+            _f32c, (means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp))
+        color, radii, depth, state = rasterize_forward(raster_settings, means3D, sh, colors_precomp, opacities,
+                                                       scales, rotations, cov3Ds_precomp)
+        ctx.raster_settings = raster_settings
+        ctx.state = state
+        ctx.has = (sh is not None, colors_precomp is not None, scales is not None, cov3Ds_precomp is not None)
+        ctx.save_for_backward(means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp, radii)
+        ctx.mark_non_differentiable(radii)
+        ctx.set_materialize_grads(False)
+        _RasterizeGaussians.last_state = state
+        return color, radii, depth
+
+    @staticmethod
+    def backward(ctx, grad_color, _grad_radii, grad_depth):
+        lib = _lib.load()
+        means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp, radii = ctx.saved_tensors
+        st = ctx.state
+        dev = means3D.device
+        N, H, W = st.N, st.H, st.W
+        keep = []
+        s = _settings_struct(ctx.raster_settings, keep)
+        grad_color = torch.zeros(3, H, W, device=dev) if grad_color is None else _f32c(grad_color)
+        grad_depth = _f32c(grad_depth)
+        M = int(sh.shape[1]) if sh is not None else 0
+        new = lambda *shape: torch.empty(*shape, dtype=torch.float32, device=dev)
+        g_means3D, g_means2D, g_densify, g_opac = new(N, 3), new(N, 3), new(N, 3), new(N, 1)
+        g_sh = new(N, M, 3) if sh is not None else None
+        g_colors = new(N, 3) if colors_precomp is not None else None
+        g_scales = new(N, 3) if scales is not None else None
+        g_rots = new(N, 4) if rotations is not None else None
+        g_cov = new(N, 6) if cov3Ds_precomp is not None else None
+        stream = torch.cuda.current_stream().cuda_stream
+        _lib.check(lib.d3g_raster_backward(
+            C.byref(s), N, C.c_uint64(st.cap), _lib.ptr(means3D), _lib.ptr(sh), M, _lib.ptr(colors_precomp),
+            _lib.ptr(scales), _lib.ptr(rotations), _lib.ptr(cov3Ds_precomp), _lib.ptr(radii), _lib.ptr(st.geom),
+            _lib.ptr(st.bin), _lib.ptr(st.img), _lib.ptr(grad_color), _lib.ptr(grad_depth), _lib.ptr(g_means3D),
+            _lib.ptr(g_means2D), _lib.ptr(g_densify), _lib.ptr(g_sh), _lib.ptr(g_colors), _lib.ptr(g_opac),
+            _lib.ptr(g_scales), _lib.ptr(g_rots), _lib.ptr(g_cov), C.c_void_p(stream)))
+        return (g_means3D, g_means2D, g_densify, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov, None)
+
+
+def rasterize_gaussians(means3D, means2D, means2D_densify, sh, colors_precomp, opacities, scales, rotations,
+                        cov3Ds_precomp, raster_settings):
+    return _RasterizeGaussians.apply(means3D, means2D, means2D_densify, sh, colors_precomp, opacities, scales,
+                                     rotations, cov3Ds_precomp, raster_settings)
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        lib = _lib.load()
+        with torch.no_grad():
+            positions = _f32c(positions)
+            view = _f32c(self.raster_settings.viewmatrix)
+            out = torch.empty(positions.shape[0], dtype=torch.uint8, device=positions.device)
+            _lib.check(lib.d3g_mark_visible(int(positions.shape[0]), _lib.ptr(positions), _lib.ptr(view),
+                                            _lib.ptr(out), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        return out.bool()
+
+    def forward(self, means3D, means2D, means2D_densify, opacities, shs=None, colors_precomp=None, scales=None,
+                rotations=None, cov3D_precomp=None):
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or (
+                (scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        return rasterize_gaussians(means3D, means2D, means2D_densify, shs, colors_precomp, opacities, scales,
+                                   rotations, cov3D_precomp, self.raster_settings)

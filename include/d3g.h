@@ -1,0 +1,207 @@
+/*
+ * d3g.h — C ABI of libd3g.so, the B200-native (sm_100a) hot path of Deformable-3D-Gaussians:
+ * time-conditioned deformation MLP -> differentiable tile-based Gaussian rasterizer, fwd + bwd.
+ *
+ * This is the drop-in boundary.  Every entry point below replaces one piece of what the reference's
+ * Python reaches through torch / its CUDA extension; reference citations are relative to
+ * /root/reference.  The reference side binds these with ctypes; the in-tree
+ * host mirror lives in deformable-3d-gaussians_b200/{rasterizer,deform,renderer}.py.
+ *
+ * Conventions
+ *  - plain C: pointers, sizes, POD structs.  No torch / C++ types.  All `float*`/`void*` data
+ *    pointers are DEVICE pointers unless the name ends in `_host`.
+ *  - all work is enqueued on the caller's `stream` (a cudaStream_t passed as void*); no hidden
+ *    synchronisation, no global state; safe from one thread per GPU.
+ *  - every function returns 0 on success or a negative d3g_status; d3g_last_error() returns a
+ *    thread-local message.  No exceptions, exit(), abort() or device traps cross the boundary.
+ *  - tensors are fp32, contiguous, row-major with the shapes of the reference call sites.
+ */
+#ifndef D3G_H_
+#define D3G_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum d3g_status {
+  D3G_OK = 0,
+  D3G_ERR_INVALID = -1,  /* bad argument combination (mirrors the reference's Python exceptions) */
+  D3G_ERR_CUDA = -2,     /* a CUDA runtime call or launch failed; message has cudaGetErrorString */
+  D3G_ERR_CAPACITY = -3, /* workspace too small for the request */
+  D3G_ERR_UNSUPPORTED = -4
+} d3g_status;
+
+const char* d3g_last_error(void);
+/* ABI version, bumped on any signature change. */
+int d3g_version(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * Rasterizer.  Replaces diff_gaussian_rasterization.{GaussianRasterizationSettings,GaussianRasterizer}
+ * as constructed at gaussian_renderer/__init__.py:53-68 and invoked at :115-124 (returning image,
+ * radii, depth).  Source of the reference extension is absent (.SUBMODULES.json:9-15).
+ * ---------------------------------------------------------------------------------------------- */
+
+/* Field-for-field the NamedTuple built at gaussian_renderer/__init__.py:53-66.  bg / viewmatrix /
+ * projmatrix / campos stay DEVICE tensors exactly as the reference passes them (no D2H copy). */
+typedef struct d3g_raster_settings {
+  int32_t image_height;
+  int32_t image_width;
+  float tanfovx;
+  float tanfovy;
+  const float* bg;         /* [3]   device */
+  float scale_modifier;
+  const float* viewmatrix; /* [4,4] device, world_view_transform as stored (transposed) */
+  const float* projmatrix; /* [4,4] device, full_proj_transform as stored */
+  int32_t sh_degree;       /* active degree, 0..3 */
+  const float* campos;     /* [3]   device */
+  int32_t prefiltered;     /* accepted, ignored (the reference always passes False, :64) */
+  int32_t debug;           /* accepted; when non-zero every launch is followed by a stream sync + check */
+  int32_t densify_mode;    /* semantics of means2D_densify.grad: 1 = same as means2D.grad,
+                              2 = component-wise sum of |per-pixel term| (default), 3 = sum of per-pixel
+                              2-norms in .x.  See DESIGN.md "open semantic #1". */
+} d3g_raster_settings;
+
+/* Workspace sizes (bytes).  geom: per-Gaussian state; img: per-pixel + per-tile state;
+ * bin: key/value double buffers + sort scratch for `pair_capacity` (tile,Gaussian) pairs. */
+int d3g_raster_geom_bytes(int32_t N, size_t* bytes);
+int d3g_raster_img_bytes(int32_t H, int32_t W, size_t* bytes);
+int d3g_raster_bin_bytes(uint64_t pair_capacity, size_t* bytes);
+
+/* Stage 1 of forward (preprocessCUDA + inclusive scan of tiles_touched).  Exactly one of shs /
+ * colors_precomp and exactly one of (scales,rotations) / cov3D_precomp must be non-NULL, as the
+ * reference's wrapper enforces.  shs is [N, sh_coeffs, 3].  radii is the [N] int32 output tensor.
+ * The number of (tile,Gaussian) pairs R is left in the geom header on the device and, when
+ * num_rendered_host (pinned) is non-NULL, copied there asynchronously on `stream`. */
+int d3g_raster_preprocess(const d3g_raster_settings* s, int32_t N, const float* means3D,
+                          const float* shs, int32_t sh_coeffs, const float* colors_precomp,
+                          const float* opacities, const float* scales, const float* rotations,
+                          const float* cov3D_precomp, void* geom, int32_t* radii,
+                          uint32_t* num_rendered_host, void* stream);
+
+/* Stage 2 of forward (duplicateWithKeys -> 64-bit tile|depth radix sort -> identifyTileRanges ->
+ * renderCUDA).  pair_capacity >= R; R itself is read on the device.  If R > pair_capacity the
+ * overflow flag readable via d3g_raster_read_header is set and the image is left undefined.
+ * out_color [3,H,W], out_depth [1,H,W]. */
+int d3g_raster_render(const d3g_raster_settings* s, int32_t N, uint64_t pair_capacity, void* geom,
+                      void* bin, void* img, const int32_t* radii, float* out_color, float* out_depth,
+                      void* stream);
+
+/* Backward (renderCUDA bwd -> computeCov2D bwd -> preprocess bwd).  Consumes the workspaces saved by
+ * forward.  dL_ddepth may be NULL (the reference never back-propagates through depth).  Any output
+ * pointer that does not apply to the chosen input mode may be NULL.  dL_dmeans2D / _densify are
+ * [N,3] (xy populated, z = 0) because scene/gaussian_model.py:398-401 reads [:, :2].  All outputs
+ * are fully written (no pre-zeroing needed). */
+int d3g_raster_backward(const d3g_raster_settings* s, int32_t N, uint64_t pair_capacity,
+                        const float* means3D, const float* shs, int32_t sh_coeffs,
+                        const float* colors_precomp, const float* scales, const float* rotations,
+                        const float* cov3D_precomp, const int32_t* radii, void* geom, void* bin,
+                        void* img, const float* dL_dcolor, const float* dL_ddepth,
+                        float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dmeans2D_densify,
+                        float* dL_dshs, float* dL_dcolors_precomp, float* dL_dopacities,
+                        float* dL_dscales, float* dL_drotations, float* dL_dcov3D_precomp,
+                        void* stream);
+
+/* Upstream `markVisible` (never called by the reference; provided for API completeness).
+ * present[i] = 1 iff view-space z > 0.2. */
+int d3g_mark_visible(int32_t N, const float* means3D, const float* viewmatrix, uint8_t* present,
+                     void* stream);
+
+/* Debug / parity access to the opaque workspaces (device -> host copies, synchronous on `stream`).
+ * which: 0 means2D[N,2] f32 | 1 depths[N] f32 | 2 conic_opacity[N,4] f32 | 3 rgb[N,3] f32 |
+ *        4 cov3D[N,6] f32 | 5 tiles_touched[N] u32 | 6 offsets[N] u32 | 7 clamped[N,3] u8 |
+ *        8 sorted keys[R] u64 | 9 point_list[R] u32 | 10 ranges[tiles,2] u32 | 11 final_T[H*W] f32 |
+ *        12 n_contrib[H*W] u32 | 13 unsorted keys[R] u64 | 14 unsorted values[R] u32
+ * header_host receives {R, overflow}. */
+int d3g_raster_read_header(const void* geom, uint32_t header_host[2], void* stream);
+int d3g_raster_read_state(int32_t which, int32_t N, int32_t H, int32_t W, uint64_t pair_capacity,
+                          const void* geom, const void* bin, const void* img, void* dst_host,
+                          size_t dst_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Deformation MLP.  Replaces DeformNetwork / DeformNetworkBaseline.forward
+ * (utils/time_utils.py:102-127, :176-201) incl. the is_6dof se(3) branch (:114-121,
+ * utils/rigid_utils.py:60-83), as called by DeformModel.step / DeformModelBaseline.step
+ * (scene/deform_model.py:260-273, :323-324).  D=8, W=256, multires=10 (the only configuration the
+ * reference instantiates, arguments/__init__.py:52-73); other shapes return D3G_ERR_UNSUPPORTED.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct d3g_mlp_config {
+  int32_t is_blender; /* timenet 13->256->30 and t_multires=6 if set, else t_multires=10 no timenet */
+  int32_t is_6dof;    /* branch_w / branch_v + exp_se3 instead of gaussian_warp */
+  int32_t heads;      /* bit0: warp (always), bit1: rotation head, bit2: scaling head.
+                         DeformNetworkBaseline = 7, DeformNetwork = 1 */
+  int32_t D, W, multires;
+} d3g_mlp_config;
+
+/* Parameter pointers in the reference's state_dict layout (utils/time_utils.py:74-100):
+ * weight [out,in] row-major, bias [out].  Unused entries NULL. */
+typedef struct d3g_mlp_params {
+  const float* timenet0_w; const float* timenet0_b; /* [256,13],[256]  (is_blender) */
+  const float* timenet2_w; const float* timenet2_b; /* [30,256],[30] */
+  const float* linear_w[8]; const float* linear_b[8]; /* [256,in_l],[256] */
+  const float* warp_w; const float* warp_b;         /* gaussian_warp [3,256] (not 6dof) */
+  const float* branch_w_w; const float* branch_w_b; /* [3,256] (6dof) */
+  const float* branch_v_w; const float* branch_v_b; /* [3,256] (6dof) */
+  const float* rot_w; const float* rot_b;           /* gaussian_rotation [4,256] */
+  const float* scale_w; const float* scale_b;       /* gaussian_scaling [3,256] */
+} d3g_mlp_params;
+
+/* Same layout, mutable: gradients are ACCUMULATED (+=) like torch .grad; caller zeroes. */
+typedef struct d3g_mlp_grads {
+  float* timenet0_w; float* timenet0_b;
+  float* timenet2_w; float* timenet2_b;
+  float* linear_w[8]; float* linear_b[8];
+  float* warp_w; float* warp_b;
+  float* branch_w_w; float* branch_w_b;
+  float* branch_v_w; float* branch_v_b;
+  float* rot_w; float* rot_b;
+  float* scale_w; float* scale_b;
+} d3g_mlp_grads;
+
+/* Bytes of the packed-weight buffer (tile images in streaming order, fwd + transposed bwd copies)
+ * and of the workspace.  With save_for_backward = 0 the workspace only holds the per-row time features
+ * and a status word; with 1 it also holds the activation / mask / gradient tile images that
+ * d3g_mlp_backward consumes (about 16.8 KB per row). */
+int d3g_mlp_packed_bytes(const d3g_mlp_config* cfg, size_t* bytes);
+int d3g_mlp_workspace_bytes(const d3g_mlp_config* cfg, int64_t rows, int32_t save_for_backward,
+                            size_t* bytes);
+
+/* Re-pack the parameters into the swizzled tile images the kernels stream (call after every
+ * optimizer step; ~4 MB, one small kernel). */
+int d3g_mlp_pack_weights(const d3g_mlp_config* cfg, const d3g_mlp_params* p, void* packed,
+                         void* stream);
+
+/* Forward for `rows` points.  xyz [rows,3].  t: [rows] with element stride t_stride (0 = one time
+ * value shared by all rows, the `fid.expand(N,1)` pattern of train_baseline.py:110).
+ * d_xyz [rows,3] or [rows,4,4] (6dof); d_rot [rows,4] / d_scale [rows,3] may be NULL when the
+ * head bit is clear. */
+int d3g_mlp_forward(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp_params* p,
+                    int64_t rows, const float* xyz, const float* t, int64_t t_stride,
+                    void* workspace, int32_t save_for_backward, float* d_xyz, float* d_rot,
+                    float* d_scale, void* stream);
+
+/* Backward.  dL_d* are the cotangents of forward's outputs (NULL = zero).  Parameter gradients are
+ * accumulated into `g`.  dL_dxyz [rows,3] and dL_dt [rows] may be NULL (every reference call site
+ * passes xyz.detach(), scene/deform_model.py callers train.py:208, train_baseline.py:115). */
+int d3g_mlp_backward(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp_params* p,
+                     int64_t rows, const float* xyz, const float* t, int64_t t_stride,
+                     void* workspace, const float* dL_dxyz_out, const float* dL_drot,
+                     const float* dL_dscale, const d3g_mlp_grads* g, float* dL_dxyz, float* dL_dt,
+                     void* stream);
+
+/* Synchronises `stream` and returns the kernels' status word (0 = ok, non-zero = an internal
+ * pipeline wait timed out, i.e. a bug).  Tests and debug mode call it; the hot path does not. */
+int d3g_mlp_read_status(const void* workspace, int32_t* status_host, void* stream);
+
+/* tcgen05 self-test used by tests/: D[128,N] = A[128,K] * B[N,K]^T through the exact smem/TMEM
+ * operand conventions the MLP kernels use.  mode 0: A,B K-major from smem; 1: A from TMEM;
+ * 2: A,B MN-major from smem (A given as [K,128], B as [K,N]). */
+int d3g_selftest_umma(int32_t mode, int32_t N, int32_t K, const float* A, const float* B, float* D,
+                      void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* D3G_H_ */

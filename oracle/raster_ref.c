@@ -131,3 +131,8 @@ uint64_t frame_fwd_bwd_f32(const cfg_f32* c, int N, const float* means3D, const 
   free(clamped); free(keys); free(vals); free(ranges); free(final_T); free(ncontrib);
   return R;
 }
+
+/* direct access to the pinned exp (accuracy test) */
+void det_exp_array_f32(int n, const float* x, float* y) {
+  for (int i = 0; i < n; i++) y[i] = det_exp_f32(x[i]);
+}

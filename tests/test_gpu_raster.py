@@ -1,0 +1,208 @@
+"""GPU parity of the rasterizer (through the C ABI) against the CPU oracle.
+
+Bars (BASELINE.json north_star): radii / tiles / keys / ranges / R bit-exact; forward image & depth
+<= 1e-4 max-abs (the pinned-op-order design gives bit-exact, which is what is asserted for final_T /
+n_contrib and, with a 1-ulp allowance, for the image); gradients <= 1e-3 relative (max|a-b|/max|b|)."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import pkg
+from oracle import raster_oracle as ro
+
+pytestmark = pytest.mark.gpu
+
+
+def _scene(N, H, W, seed=0, theta=20.0, kind="uniform", scale_mul=1.0, sh_degree=3, bg=(0.1, 0.2, 0.3)):
+    synth = pkg("synth")
+    g = synth.SynthGaussians(N, seed=seed, kind=kind, sh_degree=3)
+    g._scaling += math.log(scale_mul)
+    g.active_sh_degree = sh_degree
+    cam = synth.make_camera(W, H, theta_deg=theta)
+    return g, cam, torch.tensor(bg, dtype=torch.float32)
+
+
+def _oracle(g, cam, bg, H, W, densify_mode=2, means3D=None, colors=None, cov=None):
+    cfg = ro.make_cfg(H, W, math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5), bg.numpy(), 1.0,
+                      cam.world_view_transform.numpy(), cam.full_proj_transform.numpy(),
+                      cam.camera_center.numpy(), g.active_sh_degree, 16, densify_mode, np.float32)
+    m = g.get_xyz.numpy() if means3D is None else means3D
+    f = ro.forward(cfg, m, None if colors is not None else g.get_features.numpy(), colors, g.get_opacity.numpy(),
+                   None if cov is not None else g.get_scaling.numpy(), None if cov is not None else g.get_rotation.numpy(), cov)
+    return cfg, f
+
+
+def _gpu_forward(g, cam, bg, H, W, colors=None, cov=None, requires_grad=False):
+    rast = pkg("rasterizer")
+    synth = pkg("synth")
+    camd = synth.camera_to(cam, "cuda")
+    rs = rast.GaussianRasterizationSettings(
+        image_height=H, image_width=W, tanfovx=math.tan(cam.FoVx * 0.5), tanfovy=math.tan(cam.FoVy * 0.5),
+        bg=bg.cuda(), scale_modifier=1.0, viewmatrix=camd.world_view_transform, projmatrix=camd.full_proj_transform,
+        sh_degree=g.active_sh_degree, campos=camd.camera_center, prefiltered=False, debug=True)
+    t = lambda a: None if a is None else torch.as_tensor(a, dtype=torch.float32).cuda().requires_grad_(requires_grad)
+    inp = dict(means3D=t(g.get_xyz), shs=None if colors is not None else t(g.get_features),
+               colors_precomp=t(colors), opacities=t(g.get_opacity),
+               scales=None if cov is not None else t(g.get_scaling),
+               rotations=None if cov is not None else t(g.get_rotation), cov3D_precomp=t(cov))
+    N = g.get_xyz.shape[0]
+    m2d = torch.zeros(N, 3, device="cuda", requires_grad=True)
+    m2dd = torch.zeros(N, 3, device="cuda", requires_grad=True)
+    r = rast.GaussianRasterizer(rs)
+    color, radii, depth = r(means2D=m2d, means2D_densify=m2dd, **inp)
+    return color, radii, depth, rast._RasterizeGaussians.last_state, inp, m2d, m2dd
+
+
+def _check_forward_bitexact(f, color, radii, depth, st):
+    N, R = f["N"], f["R"]
+    assert st.R == R, "duplication count R"
+    assert np.array_equal(radii.cpu().numpy(), f["radii"]), "radii"
+    assert np.array_equal(st.read(5, torch.int32, N).numpy().view(np.uint32), f["tiles_touched"]), "tiles_touched"
+    assert np.array_equal(st.read(6, torch.int32, N).numpy().view(np.uint32), f["offsets"]), "offsets"
+    assert np.array_equal(st.read(0, torch.float32, 2 * N).numpy().reshape(N, 2).view(np.uint32),
+                          f["means2D"].view(np.uint32)), "means2D bits"
+    assert np.array_equal(st.read(1, torch.float32, N).numpy().view(np.uint32), f["depths"].view(np.uint32)), "depth bits"
+    assert np.array_equal(st.read(2, torch.float32, 4 * N).numpy().reshape(N, 4).view(np.uint32),
+                          f["conic_opacity"].view(np.uint32)), "conic bits"
+    rgbd = st.read(3, torch.float32, 4 * N).numpy().reshape(N, 4)
+    assert np.array_equal(rgbd[:, :3].view(np.uint32), f["rgb"].view(np.uint32)), "rgb bits"
+    cl = st.read(7, torch.uint8, N).numpy()
+    assert np.array_equal(cl, f["clamped"][:, 0] | (f["clamped"][:, 1] << 1) | (f["clamped"][:, 2] << 2)), "clamped"
+    if R:
+        assert np.array_equal(st.read(13, torch.int64, R).numpy().view(np.uint64), f["keys_unsorted"][:R]), "unsorted keys"
+        assert np.array_equal(st.read(8, torch.int64, R).numpy().view(np.uint64), f["keys"][:R]), "sorted keys"
+        assert np.array_equal(st.read(9, torch.int32, R).numpy().view(np.uint32), f["point_list"][:R]), "point list"
+    T = f["ranges"].shape[0]
+    assert np.array_equal(st.read(10, torch.int32, 2 * T).numpy().view(np.uint32).reshape(T, 2), f["ranges"]), "ranges"
+    H, W = f["final_T"].shape
+    assert np.array_equal(st.read(12, torch.int32, H * W).numpy().view(np.uint32).reshape(H, W), f["n_contrib"]), "n_contrib"
+    assert np.array_equal(st.read(11, torch.float32, H * W).numpy().reshape(H, W).view(np.uint32),
+                          f["final_T"].view(np.uint32)), "final_T bits"
+    c = color.detach().cpu().numpy()
+    d = depth.detach().cpu().numpy()
+    assert np.abs(c - f["color"]).max() <= 1e-4 and np.abs(d - f["depth"]).max() <= 1e-4  # the stated bar
+    assert np.array_equal(c.view(np.uint32), f["color"].view(np.uint32)), "image bit-exact"
+    assert np.array_equal(d.view(np.uint32), f["depth"].view(np.uint32)), "depth bit-exact"
+
+
+@pytest.mark.parametrize("N,H,W,kind,scale_mul,deg", [
+    (2000, 128, 128, "uniform", 1.0, 3),
+    (5000, 200, 312, "uniform", 2.0, 3),     # ragged image (not multiples of 16)
+    (3000, 160, 160, "blob", 3.0, 2),
+    (777, 64, 48, "uniform", 6.0, 0),
+    (50000, 400, 400, "blob", 1.0, 3),       # config C1
+])
+def test_forward_bit_exact(N, H, W, kind, scale_mul, deg):
+    g, cam, bg = _scene(N, H, W, seed=N, kind=kind, scale_mul=scale_mul, sh_degree=deg)
+    _, f = _oracle(g, cam, bg, H, W)
+    color, radii, depth, st, *_ = _gpu_forward(g, cam, bg, H, W)
+    _check_forward_bitexact(f, color, radii, depth, st)
+
+
+def _rel(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-30)
+
+
+@pytest.mark.parametrize("N,H,W,scale_mul,mode,with_depth", [
+    (3000, 128, 128, 2.0, 2, False), (3000, 128, 128, 2.0, 1, True), (6000, 200, 312, 1.5, 3, False),
+    (50000, 400, 400, 1.0, 2, False)])
+def test_backward_matches_oracle(N, H, W, scale_mul, mode, with_depth):
+    rast = pkg("rasterizer")
+    g, cam, bg = _scene(N, H, W, seed=N + 1, scale_mul=scale_mul)
+    cfg, f = _oracle(g, cam, bg, H, W, densify_mode=mode)
+    gen = torch.Generator().manual_seed(5)
+    dimg = torch.randn(3, H, W, generator=gen)
+    ddep = 0.1 * torch.randn(1, H, W, generator=gen) if with_depth else None
+    go = ro.backward(cfg, f, dimg.numpy(), None if ddep is None else ddep.numpy())
+    old = rast.DENSIFY_MODE
+    rast.DENSIFY_MODE = mode
+    try:
+        color, radii, depth, st, inp, m2d, m2dd = _gpu_forward(g, cam, bg, H, W, requires_grad=True)
+        loss = (color * dimg.cuda()).sum()
+        if ddep is not None:
+            loss = loss + (depth * ddep.cuda()).sum()
+        loss.backward()
+    finally:
+        rast.DENSIFY_MODE = old
+    tol = 1e-3
+    assert _rel(inp["means3D"].grad.cpu(), go["dL_dmeans3D"]) < tol
+    assert _rel(inp["shs"].grad.cpu(), go["dL_dsh"]) < tol
+    assert _rel(inp["opacities"].grad.cpu(), go["dL_dopacity"]) < tol
+    assert _rel(inp["scales"].grad.cpu(), go["dL_dscales"]) < tol
+    assert _rel(inp["rotations"].grad.cpu(), go["dL_drots"]) < tol
+    assert _rel(m2d.grad.cpu()[:, :2], go["dL_dmean2D"]) < tol
+    assert _rel(m2dd.grad.cpu()[:, :2], go["dL_dmean2D_densify"]) < tol
+    assert torch.all(m2d.grad[:, 2] == 0)
+
+
+def test_precomputed_colour_and_covariance_paths():
+    N, H, W = 2500, 96, 144
+    g, cam, bg = _scene(N, H, W, seed=9, scale_mul=2.0)
+    gen = torch.Generator().manual_seed(3)
+    colors = torch.rand(N, 3, generator=gen).numpy()
+    renderer = pkg("renderer")
+    cov = renderer._build_covariance(g.get_scaling, 1.0, g._rotation).numpy()
+    cfg, f = _oracle(g, cam, bg, H, W, colors=colors, cov=cov)
+    color, radii, depth, st, inp, m2d, m2dd = _gpu_forward(g, cam, bg, H, W, colors=colors, cov=cov, requires_grad=True)
+    assert np.array_equal(radii.cpu().numpy(), f["radii"])
+    assert np.array_equal(color.detach().cpu().numpy().view(np.uint32), f["color"].view(np.uint32))
+    dimg = torch.randn(3, H, W, generator=gen)
+    go = ro.backward(cfg, f, dimg.numpy(), None)
+    (color * dimg.cuda()).sum().backward()
+    assert _rel(inp["colors_precomp"].grad.cpu(), go["dL_dcolors_precomp"]) < 1e-3
+    assert _rel(inp["cov3D_precomp"].grad.cpu(), go["dL_dcov3D"]) < 1e-3
+    assert _rel(inp["means3D"].grad.cpu(), go["dL_dmeans3D"]) < 1e-3
+
+
+def test_edge_cases_empty_and_invisible():
+    rast = pkg("rasterizer")
+    g, cam, bg = _scene(64, 48, 80, seed=1)
+    g._xyz += 100.0
+    color, radii, depth, st, *_ = _gpu_forward(g, cam, bg, 48, 80, requires_grad=True)
+    assert st.R == 0 and torch.all(radii == 0)
+    assert torch.allclose(color[0], torch.full_like(color[0], 0.1))
+    color.sum().backward()  # must not crash with R == 0
+    # N == 0
+    g0, cam, bg = _scene(1, 32, 32)
+    for k in ("_xyz", "_scaling", "_rotation", "_opacity", "_features_dc", "_features_rest"):
+        setattr(g0, k, getattr(g0, k)[:0])
+    color, radii, depth, st, *_ = _gpu_forward(g0, cam, bg, 32, 32)
+    assert radii.numel() == 0 and torch.allclose(color[2], torch.full_like(color[2], 0.3))
+
+
+def test_argument_errors_mirror_reference():
+    rast = pkg("rasterizer")
+    g, cam, bg = _scene(10, 32, 32)
+    synth = pkg("synth")
+    camd = synth.camera_to(cam, "cuda")
+    rs = rast.GaussianRasterizationSettings(32, 32, 0.3, 0.3, bg.cuda(), 1.0, camd.world_view_transform,
+                                            camd.full_proj_transform, 3, camd.camera_center, False, False)
+    r = rast.GaussianRasterizer(rs)
+    z = torch.zeros(10, 3, device="cuda")
+    with pytest.raises(Exception, match="excatly one of either SHs or precomputed colors"):
+        r(means3D=z, means2D=z, means2D_densify=z, opacities=z[:, :1], shs=None, colors_precomp=None,
+          scales=z, rotations=torch.zeros(10, 4, device="cuda"))
+    with pytest.raises(Exception, match="scale/rotation pair or precomputed 3D covariance"):
+        r(means3D=z, means2D=z, means2D_densify=z, opacities=z[:, :1], shs=torch.zeros(10, 16, 3, device="cuda"),
+          scales=None, rotations=None, cov3D_precomp=None)
+    with pytest.raises(RuntimeError, match="CUDA device"):
+        r(means3D=z.cpu(), means2D=z, means2D_densify=z, opacities=z[:, :1].cpu(), shs=torch.zeros(10, 16, 3),
+          scales=z.cpu(), rotations=torch.zeros(10, 4))
+
+
+def test_mark_visible():
+    rast = pkg("rasterizer")
+    g, cam, bg = _scene(500, 32, 32, seed=2)
+    g._xyz[::2] += 100.0
+    synth = pkg("synth")
+    camd = synth.camera_to(cam, "cuda")
+    rs = rast.GaussianRasterizationSettings(32, 32, 0.3, 0.3, bg.cuda(), 1.0, camd.world_view_transform,
+                                            camd.full_proj_transform, 3, camd.camera_center, False, False)
+    vis = rast.GaussianRasterizer(rs).markVisible(g.get_xyz.cuda()).cpu().numpy()
+    m = cam.world_view_transform.numpy()
+    p = g.get_xyz.numpy()
+    z = p[:, 0] * m[0, 2] + p[:, 1] * m[1, 2] + p[:, 2] * m[2, 2] + m[3, 2]
+    assert np.mean(vis == (z > 0.2)) > 0.999
