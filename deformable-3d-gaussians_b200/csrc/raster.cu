@@ -904,10 +904,12 @@ int d3g_raster_preprocess(const d3g_raster_settings* s, int32_t N, const float* 
                           uint32_t* num_rendered_host, void* stream_) {
   if (int e = check_settings(s)) return e;
   cudaStream_t stream = (cudaStream_t)stream_;
-  if ((shs == nullptr) == (colors_precomp == nullptr))
+  // (empty tensors have NULL data pointers, so the either/or checks only apply when N > 0; the Python
+  // mirror performs them on the tensor objects themselves)
+  if (N > 0 && (shs == nullptr) == (colors_precomp == nullptr))
     return set_err(D3G_ERR_INVALID, "Please provide excatly one of either SHs or precomputed colors!");
-  if (((scales == nullptr || rotations == nullptr) && cov3D_precomp == nullptr) ||
-      ((scales != nullptr || rotations != nullptr) && cov3D_precomp != nullptr))
+  if (N > 0 && (((scales == nullptr || rotations == nullptr) && cov3D_precomp == nullptr) ||
+                ((scales != nullptr || rotations != nullptr) && cov3D_precomp != nullptr)))
     return set_err(D3G_ERR_INVALID,
                    "Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!");
   if (N < 0 || !geom || (N > 0 && (!means3D || !opacities || !radii)))

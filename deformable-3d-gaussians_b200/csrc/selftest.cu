@@ -9,7 +9,8 @@ namespace d3g {
 
 // mode 0: A,B K-major in smem (A given [128,K], B given [N,K])
 // mode 1: A in TMEM (written with tcgen05.st), B K-major in smem
-// mode 2: A,B MN-major in smem (A given [K,128], B given [K,N])
+// mode 2: A,B MN-major in smem (A given [K,128], B given [K,N]), 32-byte-base swizzle images
+// mode 3: A MN-major, B = all-ones K-major with N = 16 (the bias-gradient column-sum trick)
 __global__ void __launch_bounds__(128, 1)
 selftest_umma_kernel(int mode, int N, int K, const float* __restrict__ A, const float* __restrict__ B,
                      float* __restrict__ D, int* abort_flag) {
@@ -21,10 +22,11 @@ selftest_umma_kernel(int mode, int N, int K, const float* __restrict__ A, const 
   const uint32_t kpanels = (K + 31) / 32;
   uint8_t* sA = smem;
   uint32_t a_panel_stride, b_panel_stride, a_bytes;
-  if (mode == 2) {
-    a_panel_stride = (uint32_t)K * 128u;  // K rows per panel, 4 panels (M=128)
-    a_bytes = 4u * a_panel_stride;
-    b_panel_stride = (uint32_t)K * 128u;  // N/32 panels
+  if (mode >= 2) {
+    // MN-major wgrad images: [chunk of 32 points][panel][32 rows][128 B]; K padded up to chunks of 32
+    a_panel_stride = 4096u;
+    a_bytes = ((uint32_t)(K + 31) / 32u) * 4u * 4096u;
+    b_panel_stride = 4096u;
   } else {
     a_panel_stride = 128u * 128u;
     a_bytes = kpanels * a_panel_stride;
@@ -38,14 +40,18 @@ selftest_umma_kernel(int mode, int N, int K, const float* __restrict__ A, const 
     fence_barrier_init();
   }
   // stage operands
-  if (mode == 2) {
+  if (mode >= 2) {
     for (int i = tid; i < K * 128; i += 128) {
       int k = i / 128, m = i % 128;
-      *(uint32_t*)(sA + img_off(k, m, a_panel_stride)) = to_tf32(A[(size_t)k * 128 + m]);
+      *(uint32_t*)(sA + img_off_mn(k, m, 128)) = to_tf32(A[(size_t)k * 128 + m]);
     }
-    for (int i = tid; i < K * N; i += 128) {
-      int k = i / N, n = i % N;
-      *(uint32_t*)(sB + img_off(k, n, b_panel_stride)) = to_tf32(B[(size_t)k * N + n]);
+    if (mode == 2) {
+      for (int i = tid; i < K * N; i += 128) {
+        int k = i / N, n = i % N;
+        *(uint32_t*)(sB + img_off_mn(k, n, N)) = to_tf32(B[(size_t)k * N + n]);
+      }
+    } else {
+      for (int i = tid; i < 16 * 32; i += 128) ((float*)sB)[i] = 1.0f;  // ones, K-major, 16 rows x 128 B
     }
   } else {
     if (mode == 0)
@@ -79,13 +85,16 @@ selftest_umma_kernel(int mode, int N, int K, const float* __restrict__ A, const 
     tc_fence_after();
   }
   if (tid == 0) {
-    const uint32_t a_mn = mode == 2, b_mn = mode == 2;
+    const uint32_t a_mn = mode >= 2, b_mn = mode == 2;
     const uint32_t idesc = make_idesc_tf32(128, N, a_mn, b_mn);
     for (int k8 = 0; k8 < K / 8; k8++) {
       uint64_t bdesc, adesc = 0;
       if (mode == 2) {
-        adesc = make_smem_desc(smem_u32(sA) + k8 * 1024, a_panel_stride, 1024);
-        bdesc = make_smem_desc(smem_u32(sB) + k8 * 1024, b_panel_stride, 1024);
+        adesc = make_smem_desc_mn(smem_u32(sA) + (k8 / 4) * 4 * 4096 + (k8 % 4) * 1024);
+        bdesc = make_smem_desc_mn(smem_u32(sB) + (k8 / 4) * (N / 32) * 4096 + (k8 % 4) * 1024);
+      } else if (mode == 3) {
+        adesc = make_smem_desc_mn(smem_u32(sA) + (k8 / 4) * 4 * 4096 + (k8 % 4) * 1024);
+        bdesc = make_smem_desc(smem_u32(sB), 16, 1024);
       } else {
         adesc = make_smem_desc(smem_u32(sA) + (k8 / 4) * a_panel_stride + (k8 % 4) * 32, 16, 1024);
         bdesc = make_smem_desc(smem_u32(sB) + (k8 / 4) * b_panel_stride + (k8 % 4) * 32, 16, 1024);
@@ -119,8 +128,9 @@ using namespace d3g;
 extern "C" int d3g_selftest_umma(int32_t mode, int32_t N, int32_t K, const float* A, const float* B, float* D,
                                  void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
-  if (mode < 0 || mode > 2) return set_err(D3G_ERR_INVALID, "mode must be 0..2");
-  if (N < 32 || N > 256 || N % 32 || K < 8 || K > 64 || K % 8 || (mode == 1 && K % 32))
+  if (mode < 0 || mode > 3) return set_err(D3G_ERR_INVALID, "mode must be 0..3");
+  if (mode == 3 && N != 16) return set_err(D3G_ERR_INVALID, "mode 3 needs N=16");
+  if (((N < 32 || N % 32) && mode != 3) || N > 256 || K < 8 || K > 64 || K % 8 || (mode == 1 && K % 32))
     return set_err(D3G_ERR_INVALID, "unsupported self-test shape N=%d K=%d", N, K);
   int* flag = nullptr;
   D3G_CUDA_TRY(cudaMalloc(&flag, sizeof(int)));
@@ -136,5 +146,82 @@ extern "C" int d3g_selftest_umma(int32_t mode, int32_t N, int32_t K, const float
   cudaFree(flag);
   if (e != cudaSuccess) return set_err(D3G_ERR_CUDA, "self-test failed: %s", cudaGetErrorString(e));
   if (h) return set_err(D3G_ERR_CUDA, "self-test: mbarrier wait timed out (protocol error)");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Raw probe: the host supplies byte images for A and B, one (A,B) descriptor pair per MMA (start
+// address fields relative to the image base) and the instruction descriptor.  Used by
+// tests/test_gpu_umma.py to pin the shared-memory operand conventions empirically.
+// ------------------------------------------------------------------------------------------------
+namespace d3g {
+__global__ void __launch_bounds__(128, 1)
+selftest_raw_kernel(const uint8_t* __restrict__ a_img, uint32_t a_bytes, const uint8_t* __restrict__ b_img,
+                    uint32_t b_bytes, int n_mma, const uint64_t* __restrict__ adesc,
+                    const uint64_t* __restrict__ bdesc, uint32_t idesc, int N, float* __restrict__ D,
+                    int* abort_flag) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_base_s;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + ((a_bytes + 1023u) & ~1023u);
+  if (warp == 0) tmem_alloc(&tmem_base_s, 256);
+  if (tid == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
+  for (uint32_t i = tid; i < a_bytes / 4; i += 128) ((uint32_t*)sA)[i] = ((const uint32_t*)a_img)[i];
+  for (uint32_t i = tid; i < b_bytes / 4; i += 128) ((uint32_t*)sB)[i] = ((const uint32_t*)b_img)[i];
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+  if (tid == 0) {
+    for (int i = 0; i < n_mma; i++) {
+      uint64_t ad = adesc[i] + (uint64_t)((smem_u32(sA) >> 4) & 0x3FFFu);
+      uint64_t bd = bdesc[i] + (uint64_t)((smem_u32(sB) >> 4) & 0x3FFFu);
+      umma_tf32_ss(tmem_base, ad, bd, idesc, i > 0);
+    }
+    umma_commit(&bar);
+  }
+  bool ok = mbar_wait(&bar, 0, abort_flag);
+  tc_fence_after();
+  if (ok) {
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+    for (int c0 = 0; c0 < N; c0 += 32) {
+      uint32_t v[32];
+      tmem_ld32(lane_addr + c0, v);
+      tmem_wait_ld();
+#pragma unroll
+      for (int j = 0; j < 32; j++)
+        if (c0 + j < N) D[(size_t)tid * N + c0 + j] = __uint_as_float(v[j]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, 256);
+}
+}  // namespace d3g
+
+extern "C" int d3g_selftest_umma_raw(const void* a_img, uint32_t a_bytes, const void* b_img, uint32_t b_bytes,
+                                     int32_t n_mma, const uint64_t* adesc, const uint64_t* bdesc, uint32_t idesc,
+                                     int32_t N, float* D, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (a_bytes % 4 || b_bytes % 4 || a_bytes > 98304 || b_bytes > 98304 || N < 8 || N > 256 || n_mma < 1)
+    return set_err(D3G_ERR_INVALID, "unsupported raw self-test arguments");
+  int* flag = nullptr;
+  D3G_CUDA_TRY(cudaMalloc(&flag, sizeof(int)));
+  D3G_CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(int), stream));
+  size_t smem = 1024 + 98304 + 98304 + 1024;
+  D3G_CUDA_TRY(cudaFuncSetAttribute(selftest_raw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  selftest_raw_kernel<<<1, 128, smem, stream>>>((const uint8_t*)a_img, a_bytes, (const uint8_t*)b_img, b_bytes, n_mma,
+                                                adesc, bdesc, idesc, N, D, flag);
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+  int h = 0;
+  if (e == cudaSuccess) e = cudaMemcpy(&h, flag, sizeof(int), cudaMemcpyDeviceToHost);
+  cudaFree(flag);
+  if (e != cudaSuccess) return set_err(D3G_ERR_CUDA, "raw self-test failed: %s", cudaGetErrorString(e));
+  if (h) return set_err(D3G_ERR_CUDA, "raw self-test: mbarrier wait timed out");
   return 0;
 }

@@ -2,16 +2,23 @@
 // UBLKCP), tcgen05 MMA / TMEM alloc / ld / st / commit / fences, and the shared-memory operand
 // descriptors.  Everything is inline PTX; no CUTLASS.
 //
-// Operand images.  Every matrix operand lives in shared memory (and in HBM, pre-arranged the same
-// way, so a tile moves with ONE linear bulk copy and needs no tensor map) as a "panelised SWIZZLE_128B
-// image": the matrix X[r][c] (fp32) is cut into panels of 32 columns (=128 B); inside a panel row r
-// sits at byte r*128 and its eight 16-byte chunks are XOR-swizzled with (r & 7):
-//     byte(r,c) = (c/32)*panel_stride + r*128 + ((((c%32)/4) ^ (r&7)) * 16) + (c%4)*4
-// Read "K-major" (r = M/N index, c = K index) this is the canonical UMMA K-major SW128 layout with
-// SBO = 1024 B; read "MN-major" (r = K index, c = M/N index) the very same bytes are the canonical
-// MN-major SW128 layout with SBO = 1024 B (next 8 k) and LBO = panel_stride (next 32 m/n).  The MLP
-// forward/backward use the first reading, the weight-gradient kernel the second, on the same saved
-// activation images.
+// Operand images.  Two layouts are used, both pre-arranged in HBM exactly as they sit in shared memory,
+// so a tile moves with ONE linear bulk copy and needs no tensor map.
+//
+// (1) K-major "panelised SWIZZLE_128B image" (forward / input-gradient operands): the matrix X[r][c]
+//     (fp32, r = M/N index, c = K index) is cut into panels of 32 columns (=128 B); inside a panel row r
+//     sits at byte r*128 and its eight 16-byte chunks are XOR-swizzled with (r & 7):
+//         byte(r,c) = (c/32)*panel_stride + r*128 + ((((c%32)/4) ^ (r&7)) * 16) + (c%4)*4
+//     = canonical UMMA K-major SW128 layout, SBO = 1024 B, layout type 2.
+//
+// (2) MN-major "32-byte-base 128B-swizzle image" (weight-gradient operands, K = points): measured on
+//     B200 with tools/probe_umma.py — for kind::tf32 an MN-major operand reads zeros with layout types 0
+//     and 2 and works with layout type 1 (SWIZZLE_128B_BASE32B): rows of 128 B hold 32 consecutive M/N
+//     elements of one k; 4 consecutive k rows form a 512-byte atom whose four 32-byte chunks are
+//     XOR-swizzled with (k & 3); SBO = stride between 4-k atoms, LBO = stride between 32-wide M/N panels.
+//     A tile of 128 points x C features is stored as [point chunk of 32][panel C/32][32 rows][128 B]:
+//         byte(p,f) = (p/32)*(C/32)*4096 + (f/32)*4096 + (p%32)*128 + ((((f%32)/8) ^ (p&3)) * 32) + (f%8)*4
+//     so SBO = 512, LBO = 4096 and one 32-point chunk of all C features is one contiguous block.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -25,6 +32,12 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 // byte offset of element (r,c) inside a panelised SW128 image
 __device__ __host__ __forceinline__ uint32_t img_off(uint32_t r, uint32_t c, uint32_t panel_stride) {
   return (c >> 5) * panel_stride + r * 128u + ((((c & 31u) >> 2) ^ (r & 7u)) << 4) + ((c & 3u) << 2);
+}
+
+// byte offset of (point p, feature f) inside an MN-major wgrad image of a 128 x C tile
+__device__ __host__ __forceinline__ uint32_t img_off_mn(uint32_t p, uint32_t f, uint32_t C) {
+  return (p >> 5) * (C >> 5) * 4096u + (f >> 5) * 4096u + (p & 31u) * 128u + ((((f & 31u) >> 3) ^ (p & 3u)) << 5) +
+         ((f & 7u) << 2);
 }
 
 // ---- mbarrier --------------------------------------------------------------------------------
@@ -102,15 +115,24 @@ __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence:
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
 // ---- descriptors -------------------------------------------------------------------------------
-// Shared-memory matrix descriptor, SWIZZLE_128B, sm_100 version bits.
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// Shared-memory matrix descriptor, sm_100 version bits; layout type 2 = SWIZZLE_128B (K-major images),
+// 1 = SWIZZLE_128B_BASE32B (MN-major tf32 images).
+__device__ __forceinline__ uint64_t make_smem_desc_t(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                     uint32_t layout_type) {
   uint64_t d = 0;
   d |= (uint64_t)((saddr >> 4) & 0x3FFFu);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
   d |= (uint64_t)1 << 46;  // descriptor version (Blackwell)
-  d |= (uint64_t)2 << 61;  // SWIZZLE_128B
+  d |= (uint64_t)layout_type << 61;
   return d;
+}
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return make_smem_desc_t(saddr, lbo_bytes, sbo_bytes, 2u);
+}
+// MN-major wgrad image operand: start of a group of 8 points inside a 32-point chunk
+__device__ __forceinline__ uint64_t make_smem_desc_mn(uint32_t saddr) {
+  return make_smem_desc_t(saddr, 4096u, 512u, 1u);
 }
 // kind::tf32 instruction descriptor: D=f32, A=B=tf32, dense; majors: 0 = K-major, 1 = MN-major.
 __device__ __host__ __forceinline__ uint32_t make_idesc_tf32(uint32_t M, uint32_t N, uint32_t a_mn, uint32_t b_mn) {

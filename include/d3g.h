@@ -197,9 +197,17 @@ int d3g_mlp_read_status(const void* workspace, int32_t* status_host, void* strea
 
 /* tcgen05 self-test used by tests/: D[128,N] = A[128,K] * B[N,K]^T through the exact smem/TMEM
  * operand conventions the MLP kernels use.  mode 0: A,B K-major from smem; 1: A from TMEM;
- * 2: A,B MN-major from smem (A given as [K,128], B as [K,N]). */
+ * 2: A,B MN-major from smem (A given as [K,128], B as [K,N]); 3: A MN-major, B = ones (N = 16), i.e.
+ * D[m,:] = sum_k A[k,m] (the bias-gradient trick). */
 int d3g_selftest_umma(int32_t mode, int32_t N, int32_t K, const float* A, const float* B, float* D,
                       void* stream);
+
+/* Raw tcgen05 probe (tests / tools only): host-supplied operand images, one shared-memory descriptor
+ * pair per MMA (start-address field relative to the image), host-supplied instruction descriptor.
+ * D is [128,N]. */
+int d3g_selftest_umma_raw(const void* a_img, uint32_t a_bytes, const void* b_img, uint32_t b_bytes,
+                          int32_t n_mma, const uint64_t* adesc, const uint64_t* bdesc, uint32_t idesc,
+                          int32_t N, float* D, void* stream);
 
 #ifdef __cplusplus
 }

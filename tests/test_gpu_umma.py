@@ -19,7 +19,9 @@ def _run(mode, N, K):
     A += torch.arange(128).float()[:, None] * 0.01 + torch.arange(K).float()[None] * 0.1
     ref = A.double() @ B.double().T
     Ad, Bd = A.cuda(), B.cuda()
-    if mode == 2:
+    if mode == 3:
+        ref = A.double().sum(1, keepdim=True).expand(128, N)
+    if mode >= 2:
         Ad, Bd = Ad.t().contiguous(), Bd.t().contiguous()  # [K,128], [K,N]
     D = torch.full((128, N), float("nan"), device="cuda")
     _lib.check(lib.d3g_selftest_umma(mode, N, K, _lib.ptr(Ad), _lib.ptr(Bd), _lib.ptr(D),
@@ -33,6 +35,16 @@ def _run(mode, N, K):
 def test_umma_selftest(mode, N, K):
     err = _run(mode, N, K)
     assert err < 2e-3, "mode %d N=%d K=%d rel err %.3e" % (mode, N, K, err)
+
+
+@pytest.mark.parametrize("N,K", [(96, 40), (224, 64)])
+def test_umma_mn_major_odd_shapes(N, K):
+    assert _run(2, N, K) < 2e-3
+
+
+@pytest.mark.parametrize("K", [8, 32, 64])
+def test_umma_ones_column_sum(K):
+    assert _run(3, 16, K) < 2e-3
 
 
 def test_umma_k8_steps():
