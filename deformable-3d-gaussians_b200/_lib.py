@@ -103,7 +103,7 @@ MlpGrads = _ptr_struct("MlpGrads")
 EXPORTS = ["d3g_last_error", "d3g_version", "d3g_raster_geom_bytes", "d3g_raster_img_bytes",
            "d3g_raster_bin_bytes", "d3g_raster_preprocess", "d3g_raster_render", "d3g_raster_backward",
            "d3g_mark_visible", "d3g_raster_read_header", "d3g_raster_read_state", "d3g_mlp_packed_bytes",
-           "d3g_mlp_workspace_bytes", "d3g_mlp_pack_weights", "d3g_mlp_forward", "d3g_mlp_backward", "d3g_mlp_read_status",
+           "d3g_mlp_workspace_bytes", "d3g_mlp_pack_weights", "d3g_mlp_forward", "d3g_mlp_backward", "d3g_mlp_read_status", "d3g_mlp_read_masks",
            "d3g_selftest_umma", "d3g_selftest_umma_raw"]
 
 _lib = None

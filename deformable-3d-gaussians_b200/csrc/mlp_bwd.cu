@@ -1,8 +1,702 @@
-// placeholder until the backward kernels land (next commit)
+// Deformation-MLP backward for sm_100a: input-gradient chain + weight gradients, both on tcgen05.
+//
+// Reference: autograd through DeformNetwork(.Baseline).forward, utils/time_utils.py:102-127 / :176-201
+// (8x256 trunk with the skip at layer 5, heads, optional exp_se3 of utils/rigid_utils.py:60-83).
+//
+// Kernel 1 (mlp_dgrad_kernel) — same persistent / warp-specialised shape as the forward: per 128-point
+//   tile the head cotangents are gathered (and pushed back through the se(3) map for is_6dof) into a
+//   shared-memory A operand, dH_7 = dOut * W_heads, then for l = 7..1: dZ_l = dH_l (.) relu'(h_l) is
+//   formed IN PLACE in tensor memory (tcgen05.ld -> mask -> tcgen05.st) and consumed as the TMEM A
+//   operand of dH_{l-1} = dZ_l * W_l.  Each dZ_l tile is also written to HBM as an MN-major wgrad image.
+// Kernel 2 (mlp_wgrad_kernel) — dW_l = dZ_l^T * h_{l-1} is a GEMM whose K dimension is the points.
+//   Both operands are read as MN-major images straight from what forward / kernel 1 saved; CTA pairs
+//   split the 256 output features, the tile range is split-K over the pairs, partial sums leave TMEM
+//   through vector reductions (red.global.add.v4.f32) into the gradient tensors.  Bias gradients ride
+//   along as 16 extra accumulator columns (dZ^T * ones).
+// Kernel 3 (mlp_finish_kernel) — head biases and the timenet (13->256->30) backward for a shared t.
+#include <math.h>
+
 #include "mlp_common.cuh"
+
+namespace d3g {
+
+constexpr int kBwdNumStages = 5;
+constexpr int kBwdThreads = 320;
+
+struct BwdSmem {
+  static constexpr uint32_t dout = 0;                       // 16 KB K-major panel (32 columns)
+  static constexpr uint32_t stages = kPanelBytes;
+  static constexpr uint32_t headb = stages + kBwdNumStages * kStageBytes;  // 16 floats
+  static constexpr uint32_t bars = headb + 64;
+  static constexpr uint32_t total = bars + 256;
+};
+static_assert(BwdSmem::bars % 8 == 0, "barrier alignment");
+
+struct MlpBwdArgs {
+  const uint8_t* wbwd;   // transposed weight stages
+  int64_t rows;
+  int tiles;
+  int is_6dof, heads;
+  const uint32_t* mask;
+  const float* heads_out;
+  const float* g_xyz;    // [rows,3] or [rows,4,4]
+  const float* g_rot;    // [rows,4] or NULL
+  const float* g_scale;  // [rows,3] or NULL
+  uint8_t* dz_img;
+  uint8_t* dout_img;
+  float* headb_acc;      // [16] column sums of dOut
+  int* abort_flag;
+};
+
+// Cotangent of the 16 head pre-outputs of one point.  Not 6dof: [g_xyz(3) | g_rot(4) | g_scale(3)].
+// 6dof: [d w_raw(3) | d v_raw(3) | g_rot(4) | g_scale(3)], where (w_raw, v_raw) -> exp_se3 as in
+// utils/time_utils.py:114-121 (w = w_raw/theta + 1e-5, v likewise, theta = |w_raw|).
+__device__ __forceinline__ void head_cotangent(const MlpBwdArgs& a, int64_t grow, const float* ho, float (&o)[16]) {
+#pragma unroll
+  for (int j = 0; j < 16; j++) o[j] = 0.f;
+  if (!a.is_6dof) {
+    if (a.g_xyz) { o[0] = a.g_xyz[3 * grow]; o[1] = a.g_xyz[3 * grow + 1]; o[2] = a.g_xyz[3 * grow + 2]; }
+    if (a.g_rot) { float4 r = *(const float4*)(a.g_rot + 4 * grow); o[3] = r.x; o[4] = r.y; o[5] = r.z; o[6] = r.w; }
+    if (a.g_scale) { o[7] = a.g_scale[3 * grow]; o[8] = a.g_scale[3 * grow + 1]; o[9] = a.g_scale[3 * grow + 2]; }
+    return;
+  }
+  if (a.g_rot) { float4 r = *(const float4*)(a.g_rot + 4 * grow); o[6] = r.x; o[7] = r.y; o[8] = r.z; o[9] = r.w; }
+  if (a.g_scale) { o[10] = a.g_scale[3 * grow]; o[11] = a.g_scale[3 * grow + 1]; o[12] = a.g_scale[3 * grow + 2]; }
+  if (!a.g_xyz) return;
+  const float4* G4 = (const float4*)(a.g_xyz + 16 * grow);
+  float4 g0 = G4[0], g1 = G4[1], g2 = G4[2];
+  float GR[9] = {g0.x, g0.y, g0.z, g1.x, g1.y, g1.z, g2.x, g2.y, g2.z};
+  float Gp[3] = {g0.w, g1.w, g2.w};
+  float wr[3] = {ho[0], ho[1], ho[2]}, vr[3] = {ho[3], ho[4], ho[5]};
+  float theta = sqrtf(wr[0] * wr[0] + wr[1] * wr[1] + wr[2] * wr[2]);
+  float it = 1.0f / theta;
+  float w[3] = {wr[0] * it + 1e-5f, wr[1] * it + 1e-5f, wr[2] * it + 1e-5f};
+  float v[3] = {vr[0] * it + 1e-5f, vr[1] * it + 1e-5f, vr[2] * it + 1e-5f};
+  float sn, cs;
+  sincosf(theta, &sn, &cs);
+  float W[9] = {0.f, -w[2], w[1], w[2], 0.f, -w[0], -w[1], w[0], 0.f};
+  float W2[9];
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) W2[3 * i + j] = W[3 * i] * W[j] + W[3 * i + 1] * W[3 + j] + W[3 * i + 2] * W[6 + j];
+  const float c1 = 1.0f - cs, c2 = theta - sn;
+  // p = P v, P = theta I + c1 W + c2 W2;  R = I + sn W + c1 W2
+  float dP[9], dv[3] = {0.f, 0.f, 0.f};
+  float dtheta = 0.f;
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      float id = i == j ? 1.f : 0.f;
+      float Pij = theta * id + c1 * W[3 * i + j] + c2 * W2[3 * i + j];
+      dv[j] += Pij * Gp[i];
+      dP[3 * i + j] = Gp[i] * v[j];
+      // dR/dtheta = cs W + sn W2 ; dP/dtheta = I + sn W + c1 W2
+      dtheta += GR[3 * i + j] * (cs * W[3 * i + j] + sn * W2[3 * i + j]) +
+                dP[3 * i + j] * (id + sn * W[3 * i + j] + c1 * W2[3 * i + j]);
+    }
+  // cotangent of W2 and of W
+  float dW2[9], dW[9];
+#pragma unroll
+  for (int i = 0; i < 9; i++) { dW2[i] = c1 * GR[i] + c2 * dP[i]; dW[i] = sn * GR[i] + c1 * dP[i]; }
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      float acc = 0.f;
+#pragma unroll
+      for (int k = 0; k < 3; k++) acc += dW2[3 * i + k] * W[3 * j + k] + W[3 * k + i] * dW2[3 * k + j];
+      dW[3 * i + j] += acc;  // G W^T + W^T G
+    }
+  float dw[3] = {dW[7] - dW[5], dW[2] - dW[6], dW[3] - dW[1]};
+  float dot = 0.f;
+#pragma unroll
+  for (int d = 0; d < 3; d++) dot += dw[d] * wr[d] + dv[d] * vr[d];
+  dtheta -= dot * it * it;
+#pragma unroll
+  for (int d = 0; d < 3; d++) {
+    o[d] = dw[d] * it + dtheta * wr[d] * it;
+    o[3 + d] = dv[d] * it;
+  }
+}
+
+__global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* sDout = smem + BwdSmem::dout;
+  uint8_t* sStage = smem + BwdSmem::stages;
+  float* sHeadB = (float*)(smem + BwdSmem::headb);
+  uint64_t* bars = (uint64_t*)(smem + BwdSmem::bars);
+  uint64_t* full = bars;                      // [kBwdNumStages]
+  uint64_t* empty = bars + kBwdNumStages;     // [kBwdNumStages]
+  uint64_t* acc_full = bars + 2 * kBwdNumStages;
+  uint64_t* dout_ready = acc_full + 1;
+  uint64_t* a_ready = dout_ready + 1;         // [8]
+  uint32_t* tmem_slot = (uint32_t*)(a_ready + 8);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  volatile int* abort_flag = a.abort_flag;
+
+  if (tid == 0) {
+    for (int i = 0; i < kBwdNumStages; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(acc_full, 1);
+    mbar_init(dout_ready, 8);
+    for (int i = 0; i < 8; i++) mbar_init(&a_ready[i], 4);
+    fence_barrier_init();
+  }
+  if (warp == 9) tmem_alloc(tmem_slot, 512);
+  if (tid < 16) sHeadB[tid] = 0.f;
+  // the dOut panel is only ever written in its first 16 logical columns; clear it once
+  for (int i = tid; i < (int)(kPanelBytes / 16); i += kBwdThreads) ((uint4*)sDout)[i] = make_uint4(0, 0, 0, 0);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 8) {
+    // ================= weight producer (transposed stages) =================
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      bool ok = true;
+      for (int tile = blockIdx.x; ok && tile < a.tiles; tile += gridDim.x) {
+        for (int st = 0; st < kBwdStages; st++) {
+          if (!mbar_wait(&empty[s], ph ^ 1, abort_flag)) { ok = false; break; }
+          mbar_arrive_expect_tx(&full[s], kStageBytes);
+          bulk_g2s(sStage + (size_t)s * kStageBytes, a.wbwd + (size_t)st * kStageBytes, kStageBytes, &full[s]);
+          if (++s == kBwdNumStages) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 9) {
+    // ================= MMA issuer =================
+    if (lane == 0) {
+      const uint32_t idesc256 = make_idesc_tf32(128, 256, 0, 0);
+      int s = 0;
+      uint32_t ph = 0, d_ph = 0, a_ph = 0;
+      bool ok = true;
+      auto release = [&]() { umma_commit(&empty[s]); if (++s == kBwdNumStages) { s = 0; ph ^= 1; } };
+      for (int tile = blockIdx.x; ok && tile < a.tiles; tile += gridDim.x) {
+        // step 0: dH_7 = dOut[128,16] * Wheads[16,256]  (A from shared memory, K = 16)
+        if (!mbar_wait(dout_ready, d_ph, abort_flag)) { ok = false; break; }
+        d_ph ^= 1;
+        if (!mbar_wait(&full[s], ph, abort_flag)) { ok = false; break; }
+        tc_fence_after();
+        {
+          uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes);
+          uint32_t sa = smem_u32(sDout);
+#pragma unroll
+          for (int ks = 0; ks < 2; ks++)
+            umma_tf32_ss(tmem_base + 0, make_smem_desc(sa + ks * 32, 16, 1024), make_smem_desc(sb + ks * 32, 16, 1024),
+                         idesc256, ks != 0);
+          release();
+          umma_commit(acc_full);
+        }
+        // steps 1..7: dH_{7-j} = dZ_{8-j} * W_{8-j}; A = TMEM half (j-1)&1, D = half j&1
+        for (int j = 1; ok && j < 8; j++) {
+          const uint32_t d_col = (j & 1) * 256, a_col = ((j - 1) & 1) * 256;
+          for (int kc = 0; ok && kc < 8; kc++) {
+            if (!mbar_wait(&a_ready[kc], a_ph, abort_flag)) { ok = false; break; }
+            if (!mbar_wait(&full[s], ph, abort_flag)) { ok = false; break; }
+            tc_fence_after();
+            uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes);
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++)
+              umma_tf32_ts(tmem_base + d_col, tmem_base + a_col + kc * 32 + ks * 8,
+                           make_smem_desc(sb + ks * 32, 16, 1024), idesc256, (kc | ks) != 0);
+            release();
+          }
+          a_ph ^= 1;
+          if (ok) umma_commit(acc_full);
+        }
+      }
+    }
+  } else {
+    // ================= cotangent gather + epilogue warps (256 threads) =================
+    const int q = warp & 3, chalf = warp >> 2;
+    const int row = q * 32 + lane;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+    uint32_t acc_ph = 0;
+    bool ok = true;
+    for (int tile = blockIdx.x; ok && tile < a.tiles; tile += gridDim.x) {
+      const int64_t grow = (int64_t)tile * kRows + row;
+      const bool live = grow < a.rows;
+      // ---- head cotangents -> shared A panel + HBM wgrad image; column sums for the head biases ----
+      if (chalf == 0) {
+        float o[16];
+        if (live) {
+          float ho[16];
+          if (a.is_6dof) {
+            const float4* h4 = (const float4*)(a.heads_out + ((size_t)tile * kRows + row) * 16);
+            float4 h0 = h4[0], h1 = h4[1];
+            ho[0] = h0.x; ho[1] = h0.y; ho[2] = h0.z; ho[3] = h0.w; ho[4] = h1.x; ho[5] = h1.y;
+          }
+          head_cotangent(a, grow, ho, o);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; j++) o[j] = 0.f;
+        }
+        uint32_t u[16];
+#pragma unroll
+        for (int j = 0; j < 16; j++) u[j] = to_tf32(o[j]);
+#pragma unroll
+        for (int g = 0; g < 4; g++)
+          *(uint4*)(sDout + row * 128 + ((g ^ (row & 7)) << 4)) = make_uint4(u[4 * g], u[4 * g + 1], u[4 * g + 2], u[4 * g + 3]);
+        uint8_t* dst = a.dout_img + (size_t)tile * kDoutBytes + (row >> 5) * 4096 + (row & 31) * 128;
+#pragma unroll
+        for (int g = 0; g < 4; g++) {
+          uint4* d4 = (uint4*)(dst + ((g ^ (row & 3)) << 5));
+          if (g < 2) {
+            d4[0] = make_uint4(u[8 * g], u[8 * g + 1], u[8 * g + 2], u[8 * g + 3]);
+            d4[1] = make_uint4(u[8 * g + 4], u[8 * g + 5], u[8 * g + 6], u[8 * g + 7]);
+          } else {
+            d4[0] = make_uint4(0, 0, 0, 0);
+            d4[1] = make_uint4(0, 0, 0, 0);
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+          float sum = __uint_as_float(u[j]);
+#pragma unroll
+          for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
+          if (lane == 0) atomicAdd(&sHeadB[j], sum);
+        }
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(dout_ready);
+
+      // ---- 8 epilogues: dZ_l = dH_l (.) relu'(h_l), l = 7..0 ----
+      for (int j = 0; ok && j < 8; j++) {
+        const int l = 7 - j;
+        uint32_t mbits[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+          mbits[i] = a.mask[(((size_t)l * a.tiles + tile) * 8 + (chalf + 2 * i)) * 128 + row];
+        if (!mbar_wait(acc_full, acc_ph, abort_flag)) { ok = false; break; }
+        acc_ph ^= 1;
+        tc_fence_after();
+        const uint32_t half = (j & 1) * 256;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          const int c = chalf + 2 * i;
+          uint32_t v[32];
+          tmem_ld32(lane_addr + half + c * 32, v);
+          tmem_wait_ld();
+          const uint32_t bits = mbits[i];
+#pragma unroll
+          for (int k = 0; k < 32; k++) v[k] = ((bits >> k) & 1u) ? to_tf32(__uint_as_float(v[k])) : 0u;
+          if (j < 7) tmem_st32(lane_addr + half + c * 32, v);
+          uint8_t* dst = a.dz_img + ((size_t)l * a.tiles + tile) * kHBytes + (row >> 5) * 32768 + c * 4096 +
+                         (row & 31) * 128;
+#pragma unroll
+          for (int j8 = 0; j8 < 4; j8++) {
+            uint4* d4 = (uint4*)(dst + ((j8 ^ (row & 3)) << 5));
+            d4[0] = make_uint4(v[8 * j8], v[8 * j8 + 1], v[8 * j8 + 2], v[8 * j8 + 3]);
+            d4[1] = make_uint4(v[8 * j8 + 4], v[8 * j8 + 5], v[8 * j8 + 6], v[8 * j8 + 7]);
+          }
+          if (j < 7) {
+            tmem_wait_st();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&a_ready[c]);
+          }
+        }
+      }
+      tc_fence_before();
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (tid < 16) atomicAdd(&a.headb_acc[tid], sHeadB[tid]);
+  if (warp == 9) tmem_dealloc(tmem_base, 512);
+}
+
+// ================================================================================================
+// Kernel 2: weight gradients.  One work item = one (A image set, B image set) GEMM over all tiles.
+// ================================================================================================
+constexpr int kWgStages = 4;
+constexpr uint32_t kWgABytes = 16384;                 // 32 points x 128 features
+constexpr uint32_t kWgBBytes = 32768;                 // 32 points x up to 256 features
+constexpr uint32_t kWgStageBytes = kWgABytes + kWgBBytes;
+constexpr int kWgThreads = 192;                       // warp 0 producer, 1 MMA, 2..5 epilogue
+constexpr int kWgItems = 10;
+
+struct WgItem {
+  const uint8_t* a_img;   // [tiles] x 128 KB images of 256 features (dz_l, or h_7 for the heads)
+  const uint8_t* b_img;   // [tiles] x b_tile_bytes
+  uint32_t b_tile_bytes;  // 131072 (h), 49152 (pe), 16384 (dout)
+  uint32_t b_chunk_bytes; // bytes of one 32-point chunk = (N/32)*4096
+  int N;                  // 256, 96 or 32
+  int bias;               // accumulate dZ^T * ones into columns 256..271
+  int kind;               // 0: trunk layer (dW[o][col0+i]), 1: heads (transposed scatter)
+  int cost;               // relative cost per tile
+  float* dW;              // trunk: gradient of linear.l.weight
+  int ld, col0, ncols;
+  float* db;              // trunk: gradient of linear.l.bias (or NULL)
+  float* db_fresh;        // scratch copy of this call's bias gradient (layers 0 and 5) or NULL
+};
+
+struct MlpWgradArgs {
+  WgItem items[kWgItems];
+  int n_items;
+  int tiles;
+  float* head_dw[16];     // heads: gradient row pointers (NULL where the head is not evaluated)
+  int* abort_flag;
+};
+
+// tile range of item `it` that pair `pair` (of `pairs`) owns; ranges of consecutive pairs tile the item
+__device__ __forceinline__ void wg_segment(const MlpWgradArgs& a, int pair, int pairs, int it, int64_t base,
+                                           int64_t total, int& t0, int& t1) {
+  const int64_t lo = total * pair / pairs, hi = total * (pair + 1) / pairs;
+  const int64_t c = a.items[it].cost;
+  const int64_t ib = base, ie = base + c * a.tiles;
+  const int64_t s = lo > ib ? lo : ib, e = hi < ie ? hi : ie;
+  if (s >= e) { t0 = t1 = 0; return; }
+  t0 = (int)((s - ib + c - 1) / c);
+  t1 = (int)((e - ib + c - 1) / c);
+}
+
+__device__ __forceinline__ void red_add_v4f(float* addr, float x, float y, float z, float w) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
+
+__global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* sStage = smem;                                   // kWgStages x 48 KB
+  uint8_t* sOnes = smem + kWgStages * kWgStageBytes;        // 2 KB: 16 rows x 128 B of 1.0f
+  uint64_t* bars = (uint64_t*)(sOnes + 2048);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + kWgStages;
+  uint64_t* acc_full = bars + 2 * kWgStages;
+  uint64_t* acc_empty = acc_full + 1;
+  uint32_t* tmem_slot = (uint32_t*)(acc_empty + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  volatile int* abort_flag = a.abort_flag;
+  const int pair = blockIdx.x >> 1, pairs = gridDim.x >> 1, half = blockIdx.x & 1;
+
+  if (tid == 0) {
+    for (int i = 0; i < kWgStages; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(acc_full, 1);
+    mbar_init(acc_empty, 4);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  for (int i = tid; i < 512; i += kWgThreads) ((float*)sOnes)[i] = 1.0f;
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  int64_t total = 0;
+  for (int it = 0; it < a.n_items; it++) total += (int64_t)a.items[it].cost * a.tiles;
+
+  if (warp == 0) {
+    // ================= producer: one 32-point chunk of A (this CTA's half) and B per stage ==========
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      bool ok = true;
+      int64_t base = 0;
+      for (int it = 0; ok && it < a.n_items; it++) {
+        const WgItem& w = a.items[it];
+        int t0, t1;
+        wg_segment(a, pair, pairs, it, base, total, t0, t1);
+        base += (int64_t)w.cost * a.tiles;
+        for (int tile = t0; ok && tile < t1; tile++) {
+          const uint8_t* pa = w.a_img + (size_t)tile * kHBytes + half * kWgABytes;
+          const uint8_t* pb = w.b_img + (size_t)tile * w.b_tile_bytes;
+          for (int ch = 0; ch < 4; ch++) {
+            if (!mbar_wait(&empty[s], ph ^ 1, abort_flag)) { ok = false; break; }
+            uint8_t* dst = sStage + (size_t)s * kWgStageBytes;
+            mbar_arrive_expect_tx(&full[s], kWgABytes + w.b_chunk_bytes);
+            bulk_g2s(dst, pa + (size_t)ch * 32768, kWgABytes, &full[s]);
+            bulk_g2s(dst + kWgABytes, pb + (size_t)ch * w.b_chunk_bytes, w.b_chunk_bytes, &full[s]);
+            if (++s == kWgStages) { s = 0; ph ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0, e_ph = 0;
+      bool ok = true;
+      int64_t base = 0;
+      const uint32_t idesc_ones = make_idesc_tf32(128, 16, 1, 0);
+      const uint64_t ones_desc = make_smem_desc(smem_u32(sOnes), 16, 1024);
+      for (int it = 0; ok && it < a.n_items; it++) {
+        const WgItem& w = a.items[it];
+        int t0, t1;
+        wg_segment(a, pair, pairs, it, base, total, t0, t1);
+        base += (int64_t)w.cost * a.tiles;
+        if (t0 >= t1) continue;
+        const uint32_t idesc = make_idesc_tf32(128, (uint32_t)w.N, 1, 1);
+        // the previous segment's accumulator must have been drained
+        if (!mbar_wait(acc_empty, e_ph ^ 1, abort_flag)) { ok = false; break; }
+        tc_fence_after();
+        uint32_t first = 1;
+        for (int tile = t0; ok && tile < t1; tile++) {
+          for (int ch = 0; ch < 4; ch++) {
+            if (!mbar_wait(&full[s], ph, abort_flag)) { ok = false; break; }
+            tc_fence_after();
+            const uint32_t sa = smem_u32(sStage + (size_t)s * kWgStageBytes), sb = sa + kWgABytes;
+#pragma unroll
+            for (int k8 = 0; k8 < 4; k8++) {
+              const uint64_t ad = make_smem_desc_mn(sa + k8 * 1024);
+              umma_tf32_ss(tmem_base, ad, make_smem_desc_mn(sb + k8 * 1024), idesc, first ? 0u : 1u);
+              if (w.bias) umma_tf32_ss(tmem_base + 256, ad, ones_desc, idesc_ones, first ? 0u : 1u);
+              first = 0;
+            }
+            umma_commit(&empty[s]);
+            if (++s == kWgStages) { s = 0; ph ^= 1; }
+          }
+        }
+        if (ok) { umma_commit(acc_full); e_ph ^= 1; }
+      }
+    }
+  } else {
+    // ================= epilogue: TMEM -> reductions into the gradient tensors =================
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    const int o = half * 128 + q * 32 + lane;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+    uint32_t f_ph = 0;
+    bool ok = true;
+    int64_t base = 0;
+    for (int it = 0; ok && it < a.n_items; it++) {
+      const WgItem& w = a.items[it];
+      int t0, t1;
+      wg_segment(a, pair, pairs, it, base, total, t0, t1);
+      base += (int64_t)w.cost * a.tiles;
+      if (t0 >= t1) continue;
+      if (!mbar_wait(acc_full, f_ph, abort_flag)) { ok = false; break; }
+      f_ph ^= 1;
+      tc_fence_after();
+      for (int c0 = 0; c0 < w.N; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(lane_addr + c0, v);
+        tmem_wait_ld();
+        if (w.kind == 0) {
+          float* dst = w.dW + (size_t)o * w.ld + w.col0 + c0;
+#pragma unroll
+          for (int j = 0; j < 8; j++) {
+            float* p4 = dst + 4 * j;
+            if (c0 + 4 * j + 3 < w.ncols && (((uintptr_t)p4) & 15) == 0) {
+              red_add_v4f(p4, __uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
+                          __uint_as_float(v[4 * j + 3]));
+            } else {
+#pragma unroll
+              for (int e = 0; e < 4; e++)
+                if (c0 + 4 * j + e < w.ncols) atomicAdd(p4 + e, __uint_as_float(v[4 * j + e]));
+            }
+          }
+        } else {
+          // heads: D[in-feature o][head j] -> d(head weight row j)[o]
+#pragma unroll
+          for (int j = 0; j < 16; j++)
+            if (a.head_dw[j]) atomicAdd(a.head_dw[j] + o, __uint_as_float(v[j]));
+        }
+      }
+      if (w.bias) {
+        uint32_t v[16];
+        tmem_ld16(lane_addr + 256, v);
+        tmem_wait_ld();
+        float g = __uint_as_float(v[0]);
+        if (w.db) atomicAdd(w.db + o, g);
+        if (w.db_fresh) atomicAdd(w.db_fresh + o, g);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(acc_empty);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+// ================================================================================================
+// Kernel 3: head-bias gradients, and the timenet backward when all rows share one time value.
+//   t-feature columns 63..92 of the pe block feed layer 0 and the skip layer, so with a shared t
+//   d tfeat[j] = sum_o db_0[o] W_0[o][63+j] + db_5[o] W_5[o][63+j]   (db = this call's bias gradients),
+//   then utils/time_utils.py:74-76 backwards: tfeat = W2 relu(W0t e + b0t) + b2.
+// ================================================================================================
+struct MlpFinishArgs {
+  const float* headb_acc;   // [16]
+  float* head_db[16];       // gradient element pointers (NULL where absent)
+  int is_blender;
+  const float* db_fresh;    // [2][256]
+  const float* w0;          // linear.0.weight [256, pe_dim]
+  const float* w5;          // linear.5.weight [256, pe_dim+256]
+  int pe_dim;
+  const float* t;           // shared time value
+  const float* thidden;     // [256] post-ReLU timenet hidden
+  const float* tn2_w;       // timenet.2.weight [30,256]
+  float* g_tn0_w; float* g_tn0_b; float* g_tn2_w; float* g_tn2_b;
+};
+
+__global__ void __launch_bounds__(256) mlp_finish_kernel(MlpFinishArgs a) {
+  __shared__ float dtf[32];
+  __shared__ float e[16];
+  const int tid = threadIdx.x;
+  if (tid < 16 && a.head_db[tid]) *a.head_db[tid] += a.headb_acc[tid];
+  if (!a.is_blender) return;
+  if (tid < 13) {
+    float tv = a.t[0];
+    float v = tv;
+    if (tid > 0) {
+      int f = (tid - 1) >> 1;
+      float arg = tv * (float)(1 << f);
+      v = ((tid - 1) & 1) ? cosf(arg) : sinf(arg);
+    }
+    e[tid] = v;
+  }
+  {
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int j = warp; j < 30; j += 8) {
+      float acc = 0.f;
+      for (int o = lane; o < 256; o += 32)
+        acc += a.db_fresh[o] * a.w0[(size_t)o * a.pe_dim + 63 + j] +
+               a.db_fresh[256 + o] * a.w5[(size_t)o * (a.pe_dim + 256) + 63 + j];
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+      if (lane == 0) dtf[j] = acc;
+    }
+  }
+  __syncthreads();
+  // thread k owns hidden unit k
+  const int k = tid;
+  const float hk = a.thidden[k];
+  float dh = 0.f;
+  for (int i = 0; i < 30; i++) {
+    a.g_tn2_w[i * 256 + k] += dtf[i] * hk;
+    dh += a.tn2_w[i * 256 + k] * dtf[i];
+  }
+  if (k < 30) a.g_tn2_b[k] += dtf[k];
+  if (!(hk > 0.f)) dh = 0.f;
+  a.g_tn0_b[k] += dh;
+  for (int c = 0; c < 13; c++) a.g_tn0_w[k * 13 + c] += dh * e[c];
+}
+
+}  // namespace d3g
+
 using namespace d3g;
-extern "C" int d3g_mlp_backward(const d3g_mlp_config*, const void*, const d3g_mlp_params*, int64_t, const float*,
-                                const float*, int64_t, void*, const float*, const float*, const float*,
-                                const d3g_mlp_grads*, float*, float*, void*) {
-  return set_err(D3G_ERR_UNSUPPORTED, "d3g_mlp_backward: not built yet");
+
+extern "C" int d3g_mlp_backward(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp_params* p,
+                                int64_t rows, const float* xyz, const float* t, int64_t t_stride, void* workspace,
+                                const float* dL_dxyz_out, const float* dL_drot, const float* dL_dscale,
+                                const d3g_mlp_grads* g, float* dL_dxyz, float* dL_dt, void* stream_) {
+  if (int e = check_cfg(cfg)) return e;
+  if (!packed || !p || !workspace || !g) return set_err(D3G_ERR_INVALID, "NULL argument");
+  if (rows < 0 || (rows > 0 && (!xyz || !t))) return set_err(D3G_ERR_INVALID, "NULL tensor");
+  if (dL_dxyz || dL_dt)
+    return set_err(D3G_ERR_UNSUPPORTED,
+                   "gradients w.r.t. xyz / t are not implemented (every reference call site passes xyz.detach())");
+  if (cfg->is_blender && t_stride != 0 && rows > 1)
+    return set_err(D3G_ERR_UNSUPPORTED, "timenet backward with per-row time values is not implemented");
+  for (int l = 0; l < 8; l++)
+    if (!g->linear_w[l] || !g->linear_b[l]) return set_err(D3G_ERR_INVALID, "linear.%d gradient buffers missing", l);
+  if (cfg->is_blender && (!g->timenet0_w || !g->timenet0_b || !g->timenet2_w || !g->timenet2_b))
+    return set_err(D3G_ERR_INVALID, "timenet gradient buffers missing");
+  if (rows == 0) return 0;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  MlpWs ws = mlp_ws_view(workspace, rows, true);
+  const int tiles = (int)((rows + kRows - 1) / kRows);
+  const int pe_dim = cfg->is_blender ? 93 : 84;
+  D3G_CUDA_TRY(cudaMemsetAsync(ws.scratch, 0, kScratchFloats * 4, stream));
+  float* headb_acc = ws.scratch;
+  float* db_fresh = ws.scratch + 16;
+
+  // ---- kernel 1: input-gradient chain ----
+  {
+    MlpBwdArgs a;
+    a.wbwd = (const uint8_t*)packed + kBwdOff;
+    a.rows = rows; a.tiles = tiles; a.is_6dof = cfg->is_6dof; a.heads = cfg->heads;
+    a.mask = ws.mask; a.heads_out = ws.heads_out;
+    a.g_xyz = dL_dxyz_out;
+    a.g_rot = (cfg->heads & 2) ? dL_drot : nullptr;
+    a.g_scale = (cfg->heads & 4) ? dL_dscale : nullptr;
+    a.dz_img = ws.dz_img; a.dout_img = ws.dout_img; a.headb_acc = headb_acc; a.abort_flag = ws.status;
+    size_t smem = BwdSmem::total + 1024;
+    D3G_CUDA_TRY(cudaFuncSetAttribute(mlp_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = tiles < num_sms() ? tiles : num_sms();
+    mlp_dgrad_kernel<<<grid, kBwdThreads, smem, stream>>>(a);
+    D3G_LAUNCH_CHECK(0, stream);
+  }
+  // ---- kernel 2: weight gradients ----
+  {
+    MlpWgradArgs a;
+    memset(&a, 0, sizeof(a));
+    a.tiles = tiles; a.abort_flag = ws.status;
+    const size_t layer_stride = (size_t)tiles * kHBytes;
+    int n = 0;
+    auto trunk = [&](int l, const uint8_t* b_img, uint32_t b_tile, int N, int bias, int col0, int ncols, int cost) {
+      WgItem& w = a.items[n++];
+      w.a_img = ws.dz_img + (size_t)l * layer_stride;
+      w.b_img = b_img; w.b_tile_bytes = b_tile; w.b_chunk_bytes = (uint32_t)(N / 32) * 4096u; w.N = N;
+      w.bias = bias; w.kind = 0; w.cost = cost;
+      w.dW = g->linear_w[l]; w.ld = l == 0 ? pe_dim : (l == 5 ? pe_dim + 256 : 256); w.col0 = col0; w.ncols = ncols;
+      w.db = bias ? g->linear_b[l] : nullptr;
+      w.db_fresh = (bias && l == 0) ? db_fresh : ((bias && l == 5) ? db_fresh + 256 : nullptr);
+    };
+    for (int l = 7; l >= 1; l--)
+      trunk(l, ws.h_img + (size_t)(l - 1) * layer_stride, kHBytes, 256, 1, l == 5 ? pe_dim : 0, 256, 272);
+    trunk(0, ws.pe_img, kPeBytes, 96, 1, 0, pe_dim, 112);
+    trunk(5, ws.pe_img, kPeBytes, 96, 0, 0, pe_dim, 96);
+    {
+      WgItem& w = a.items[n++];
+      w.a_img = ws.h_img + (size_t)7 * layer_stride;
+      w.b_img = ws.dout_img; w.b_tile_bytes = kDoutBytes; w.b_chunk_bytes = 4096; w.N = 32;
+      w.bias = 0; w.kind = 1; w.cost = 32;
+    }
+    a.n_items = n;
+    d3g_mlp_params gp;  // the gradient struct has the same layout; reuse head_map on it
+    memcpy(&gp, g, sizeof(gp));
+    HeadMap hm = head_map(*cfg, gp);
+    for (int j = 0; j < 16; j++) a.head_dw[j] = hm.w[j] ? (float*)hm.w[j] + (size_t)hm.r[j] * 256 : nullptr;
+    size_t smem = (size_t)kWgStages * kWgStageBytes + 2048 + 256 + 1024;
+    D3G_CUDA_TRY(cudaFuncSetAttribute(mlp_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = num_sms() & ~1;
+    if (grid < 2) grid = 2;
+    mlp_wgrad_kernel<<<grid, kWgThreads, smem, stream>>>(a);
+    D3G_LAUNCH_CHECK(0, stream);
+    // ---- kernel 3 ----
+    MlpFinishArgs f;
+    memset(&f, 0, sizeof(f));
+    f.headb_acc = headb_acc;
+    for (int j = 0; j < 16; j++) f.head_db[j] = hm.b[j] ? (float*)hm.b[j] + hm.r[j] : nullptr;
+    f.is_blender = cfg->is_blender;
+    f.db_fresh = db_fresh; f.w0 = p->linear_w[0]; f.w5 = p->linear_w[5]; f.pe_dim = pe_dim;
+    f.t = t; f.thidden = ws.thidden; f.tn2_w = p->timenet2_w;
+    f.g_tn0_w = g->timenet0_w; f.g_tn0_b = g->timenet0_b; f.g_tn2_w = g->timenet2_w; f.g_tn2_b = g->timenet2_b;
+    mlp_finish_kernel<<<1, 256, 0, stream>>>(f);
+    D3G_LAUNCH_CHECK(0, stream);
+  }
+  return 0;
+}
+
+// Parity / debug access: activation pattern of trunk layer `layer` as saved by a forward with
+// save_for_backward = 1.  dst_host[row*8 + c] bit j = (h_layer[row][c*32+j] > 0).  Synchronous.
+extern "C" int d3g_mlp_read_masks(const d3g_mlp_config* cfg, const void* workspace, int64_t rows, int32_t layer,
+                                  uint32_t* dst_host, void* stream_) {
+  if (int e = check_cfg(cfg)) return e;
+  if (!workspace || !dst_host || rows <= 0 || layer < 0 || layer > 7) return set_err(D3G_ERR_INVALID, "bad arguments");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  MlpWs ws = mlp_ws_view((void*)workspace, rows, true);
+  const size_t tiles = (size_t)((rows + kRows - 1) / kRows);
+  uint32_t* tmp = (uint32_t*)malloc(tiles * 8 * 128 * 4);
+  if (!tmp) return set_err(D3G_ERR_CAPACITY, "out of host memory");
+  cudaError_t e = cudaMemcpyAsync(tmp, ws.mask + (size_t)layer * tiles * 8 * 128, tiles * 8 * 128 * 4,
+                                  cudaMemcpyDeviceToHost, stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+  if (e != cudaSuccess) { free(tmp); return set_err(D3G_ERR_CUDA, "mask read failed: %s", cudaGetErrorString(e)); }
+  for (int64_t r = 0; r < rows; r++)
+    for (int c = 0; c < 8; c++) dst_host[r * 8 + c] = tmp[((size_t)(r / kRows) * 8 + c) * 128 + (r % kRows)];
+  free(tmp);
+  return 0;
 }

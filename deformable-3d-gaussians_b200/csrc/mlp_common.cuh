@@ -43,23 +43,24 @@ __host__ __device__ inline void bwd_stage_info(int st, int& layer, int& kpanel) 
 }
 
 // ---- workspace layout -------------------------------------------------------------------------
+// Saved tiles are "MN-major wgrad images" (umma.cuh, layout (2)): exactly what the weight-gradient
+// kernel feeds to the tensor core as operands with K = points, so backward never re-arranges them.
 struct MlpWs {
   int32_t* status;     // [0] abort flag
   float* tfeat;        // [rows_t, 32]   time feature fed into pe columns 63..
   float* thidden;      // [rows_t, 256]  timenet hidden (post-ReLU), blender only
-  uint8_t* pe_img;     // [tiles] x 48 KB
-  uint8_t* h_img;      // [8][tiles] x 128 KB   post-ReLU activations h_0..h_7 (tf32-rounded)
+  uint8_t* pe_img;     // [tiles] x 48 KB            pe block (96 columns)
+  uint8_t* h_img;      // [8][tiles] x 128 KB        post-ReLU activations h_0..h_7 (tf32-rounded)
   uint32_t* mask;      // [8][tiles][8 chunks][128 rows]  bit j = (h[row][chunk*32+j] > 0)
   float* heads_out;    // [tiles*128, 16] head pre-outputs (incl. bias)
-  uint8_t* dz_img;     // [8][tiles] x 128 KB   dL/d(pre-activation) tiles, written by backward
-  uint8_t* dout_img;   // [tiles] x 16 KB       head cotangents as a 32-column panel
-  float* partial;      // weight-gradient split-K partials
-  size_t partial_floats;
+  uint8_t* dz_img;     // [8][tiles] x 128 KB        dL/d(pre-activation) tiles, written by backward
+  uint8_t* dout_img;   // [tiles] x 16 KB            head cotangents (32 columns, 16 used)
+  float* scratch;      // kScratchFloats: head-bias sums [16] | fresh bias grads of layer 0 / 5 [2][256]
   size_t total;
 };
 
-constexpr int kWgradSlots = 160;                 // upper bound on split-K work items
-constexpr size_t kWgradSlotFloats = 128 * 384;   // 128 out-features x (352 in + 16 bias + pad)
+constexpr int kScratchFloats = 16 + 512 + 48;
+constexpr uint32_t kDoutBytes = 4 * 4096;
 
 inline MlpWs mlp_ws_view(void* base, int64_t rows, bool save) {
   MlpWs w;
@@ -78,15 +79,38 @@ inline MlpWs mlp_ws_view(void* base, int64_t rows, bool save) {
     w.mask = (uint32_t*)take(8 * tiles * 8 * 128 * 4);
     w.heads_out = (float*)take(tiles * 128 * 16 * 4);
     w.dz_img = (uint8_t*)take(8 * tiles * (size_t)kHBytes);
-    w.dout_img = (uint8_t*)take(tiles * (size_t)kPanelBytes);
-    w.partial_floats = (size_t)kWgradSlots * kWgradSlotFloats;
-    w.partial = (float*)take(w.partial_floats * 4);
+    w.dout_img = (uint8_t*)take(tiles * (size_t)kDoutBytes);
+    w.scratch = (float*)take(kScratchFloats * 4);
   } else {
     w.pe_img = w.h_img = w.dz_img = w.dout_img = nullptr;
-    w.mask = nullptr; w.heads_out = nullptr; w.partial = nullptr; w.partial_floats = 0;
+    w.mask = nullptr; w.heads_out = nullptr; w.scratch = nullptr;
   }
   w.total = off;
   return w;
+}
+
+// head index (row of the padded 16-wide head block) -> source parameter row
+struct HeadMap {
+  const float* w[16];
+  const float* b[16];
+  int r[16];
+};
+inline HeadMap head_map(const d3g_mlp_config& cfg, const d3g_mlp_params& p) {
+  HeadMap m;
+  for (int h = 0; h < 16; h++) {
+    m.w[h] = nullptr; m.b[h] = nullptr; m.r[h] = 0;
+    if (!cfg.is_6dof) {
+      if (h < 3) { m.w[h] = p.warp_w; m.b[h] = p.warp_b; m.r[h] = h; }
+      else if (h < 7) { if (cfg.heads & 2) { m.w[h] = p.rot_w; m.b[h] = p.rot_b; m.r[h] = h - 3; } }
+      else if (h < 10) { if (cfg.heads & 4) { m.w[h] = p.scale_w; m.b[h] = p.scale_b; m.r[h] = h - 7; } }
+    } else {
+      if (h < 3) { m.w[h] = p.branch_w_w; m.b[h] = p.branch_w_b; m.r[h] = h; }
+      else if (h < 6) { m.w[h] = p.branch_v_w; m.b[h] = p.branch_v_b; m.r[h] = h - 3; }
+      else if (h < 10) { if (cfg.heads & 2) { m.w[h] = p.rot_w; m.b[h] = p.rot_b; m.r[h] = h - 6; } }
+      else if (h < 13) { if (cfg.heads & 4) { m.w[h] = p.scale_w; m.b[h] = p.scale_b; m.r[h] = h - 10; } }
+    }
+  }
+  return m;
 }
 
 int check_cfg(const d3g_mlp_config* cfg);

@@ -193,56 +193,66 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
     const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
     uint32_t acc_ph = 0;
     bool ok = true;
-    bool store_pending = false;
     for (int tile = blockIdx.x; ok && tile < a.tiles; tile += gridDim.x) {
       const int64_t grow = (int64_t)tile * kRows + row;
       const bool live = grow < a.rows;
-      // ---- positional encoding block -> shared memory (K-major SW128 image, 3 panels) ----
-      if (store_pending) {  // previous tile's pe image is still being read by the bulk store
-        if (tid == 0) bulk_wait_read<0>();
-        named_bar_sync(1, 256);
-        store_pending = false;
-      }
+      // ---- positional encoding block: each row is built by two threads (columns 0..47 / 48..95) in
+      // registers, then written to shared memory (K-major SW128 image, A operand of layer 0 and of the
+      // skip layer) and, when saving for backward, to HBM as an MN-major wgrad image ----
       {
         float x[3] = {0.f, 0.f, 0.f};
         if (live) { x[0] = a.xyz[3 * grow]; x[1] = a.xyz[3 * grow + 1]; x[2] = a.xyz[3 * grow + 2]; }
-        auto put = [&](int col, float v) { *(uint32_t*)(sPE + img_off(row, col, kPanelBytes)) = to_tf32(v); };
+        float pe[48];
         if (chalf == 0) {
-          put(0, x[0]); put(1, x[1]); put(2, x[2]);
-          for (int f = 0; f < 5; f++) {
+          pe[0] = x[0]; pe[1] = x[1]; pe[2] = x[2];
+#pragma unroll
+          for (int f = 0; f < 8; f++) {
             float fr = (float)(1 << f);
 #pragma unroll
             for (int d = 0; d < 3; d++) {
               float sn, cs;
               sincosf(x[d] * fr, &sn, &cs);
-              put(3 + 6 * f + d, sn);
-              put(3 + 6 * f + 3 + d, cs);
+              pe[3 + 6 * f + d] = sn;
+              if (f < 7) pe[3 + 6 * f + 3 + d] = cs;
             }
           }
         } else {
-          for (int f = 5; f < 10; f++) {
+#pragma unroll
+          for (int f = 7; f < 10; f++) {
             float fr = (float)(1 << f);
 #pragma unroll
             for (int d = 0; d < 3; d++) {
               float sn, cs;
               sincosf(x[d] * fr, &sn, &cs);
-              put(3 + 6 * f + d, sn);
-              put(3 + 6 * f + 3 + d, cs);
+              if (f > 7) pe[6 * (f - 8) + 3 + d] = sn;
+              pe[6 * (f - 8) + 6 + d] = cs;
             }
           }
           const float* tf = a.tfeat + (live ? grow * a.tfeat_stride : 0);
-          for (int j = 0; j < 33; j++) put(63 + j, (live && j < a.t_dim) ? tf[j] : 0.f);
+#pragma unroll
+          for (int j = 0; j < 33; j++) pe[15 + j] = (live && j < a.t_dim) ? tf[j] : 0.f;
+        }
+        uint32_t u[48];
+#pragma unroll
+        for (int j = 0; j < 48; j++) u[j] = to_tf32(pe[j]);
+#pragma unroll
+        for (int g = 0; g < 12; g++) {
+          const uint32_t col0 = chalf * 48 + 4 * g;
+          *(uint4*)(sPE + (col0 >> 5) * kPanelBytes + row * 128 + ((((col0 & 31u) >> 2) ^ (row & 7)) << 4)) =
+              make_uint4(u[4 * g], u[4 * g + 1], u[4 * g + 2], u[4 * g + 3]);
+        }
+        if (a.save) {
+          uint8_t* dst = a.pe_img + (size_t)tile * kPeBytes + (row >> 5) * 3 * 4096 + (row & 31) * 128;
+#pragma unroll
+          for (int g = 0; g < 6; g++) {
+            const uint32_t col0 = chalf * 48 + 8 * g;
+            uint4* d4 = (uint4*)(dst + (col0 >> 5) * 4096 + ((((col0 & 31u) >> 3) ^ (row & 3)) << 5));
+            d4[0] = make_uint4(u[8 * g], u[8 * g + 1], u[8 * g + 2], u[8 * g + 3]);
+            d4[1] = make_uint4(u[8 * g + 4], u[8 * g + 5], u[8 * g + 6], u[8 * g + 7]);
+          }
         }
       }
       fence_proxy_async();
-      if (a.save) {
-        named_bar_sync(1, 256);
-        if (tid == 0) {
-          bulk_s2g(a.pe_img + (size_t)tile * kPeBytes, sPE, kPeBytes);
-          bulk_commit();
-        }
-        store_pending = true;
-      }
       __syncwarp();
       if (lane == 0) mbar_arrive(pe_ready);
 
@@ -267,10 +277,14 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
           }
           tmem_st32(lane_addr + half + c * 32, v);
           if (a.save) {
-            uint8_t* dst = a.h_img + ((size_t)l * a.tiles + tile) * kHBytes + (size_t)c * kPanelBytes + row * 128;
+            uint8_t* dst = a.h_img + ((size_t)l * a.tiles + tile) * kHBytes + (row >> 5) * 32768 + c * 4096 +
+                           (row & 31) * 128;
 #pragma unroll
-            for (int j4 = 0; j4 < 8; j4++)
-              *(uint4*)(dst + ((j4 ^ (row & 7)) << 4)) = make_uint4(v[4 * j4], v[4 * j4 + 1], v[4 * j4 + 2], v[4 * j4 + 3]);
+            for (int j8 = 0; j8 < 4; j8++) {
+              uint4* d4 = (uint4*)(dst + ((j8 ^ (row & 3)) << 5));
+              d4[0] = make_uint4(v[8 * j8], v[8 * j8 + 1], v[8 * j8 + 2], v[8 * j8 + 3]);
+              d4[1] = make_uint4(v[8 * j8 + 4], v[8 * j8 + 5], v[8 * j8 + 6], v[8 * j8 + 7]);
+            }
             a.mask[(((size_t)l * a.tiles + tile) * 8 + c) * 128 + row] = bits;
           }
           tmem_wait_st();
@@ -339,7 +353,6 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
       }
       tc_fence_before();
     }
-    if (store_pending && tid == 0) bulk_wait_all<0>();
   }
   tc_fence_before();
   __syncthreads();

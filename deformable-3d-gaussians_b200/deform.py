@@ -53,7 +53,7 @@ def _fill_ptr_struct(struct, named):
 
 class _FusedDeform(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, net, xyz, t, *params):
+    def forward(ctx, net, need_grad, xyz, t, *params):
         lib = _lib.load()
         dev = xyz.device
         if dev.type != "cuda":
@@ -71,7 +71,6 @@ class _FusedDeform(torch.autograd.Function):
             t_stride = int(t2.stride(0))
         cfg = net._cfg()
         packed = net._packed(dev)
-        need_grad = torch.is_grad_enabled() and (any(p.requires_grad for p in params) or xyz.requires_grad)
         wsb = C.c_size_t()
         _lib.check(lib.d3g_mlp_workspace_bytes(C.byref(cfg), rows, int(need_grad), C.byref(wsb)))
         ws = torch.empty(wsb.value, dtype=torch.uint8, device=dev)
@@ -124,6 +123,7 @@ class _FusedDeform(torch.autograd.Function):
                                         _lib.ptr(dxyz_in), C.c_void_p(0), C.c_void_p(stream)))
         if net.debug:
             net._check_status(ctx.ws)
+        _FusedDeform.last_ws = ctx.ws if net.debug else None  # parity inspection hook (tools/dbg_mlp_bwd.py)
         ctx.ws = None
         # heads the network never evaluates get no gradient at all (like autograd in the reference), so
         # Adam's weight decay does not touch them
@@ -133,7 +133,7 @@ class _FusedDeform(torch.autograd.Function):
         if not net._heads & HEAD_SCALE:
             unused |= {"scale_w", "scale_b"}
         out = tuple(None if n in unused else g for (n, _), g in zip(named, grads))
-        return (None, dxyz_in, None) + out
+        return (None, None, dxyz_in, None) + out
 
 
 class _DeformBase(nn.Module):
@@ -207,9 +207,25 @@ class _DeformBase(nn.Module):
         if st.value != 0:
             raise _lib.D3GError("fused MLP kernel reported an internal pipeline timeout (status %d)" % st.value)
 
+    def read_activation_masks(self, ws, rows):
+        """Parity hook: [8, rows, 256] bool activation pattern saved by the last training-mode forward."""
+        lib = _lib.load()
+        cfg = self._cfg()
+        out = np.zeros((8, rows, 256), dtype=bool)
+        buf = np.zeros(rows * 8, dtype=np.uint32)
+        for l in range(8):
+            _lib.check(lib.d3g_mlp_read_masks(C.byref(cfg), _lib.ptr(ws), C.c_int64(rows), l,
+                                              buf.ctypes.data_as(C.c_void_p),
+                                              C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+            bits = (buf.reshape(rows, 8, 1) >> np.arange(32, dtype=np.uint32).reshape(1, 1, 32)) & 1
+            out[l] = bits.reshape(rows, 256).astype(bool)
+        return out
+
     def _run(self, x, t):
         params = [p for _, p in _param_list(self)]
-        return _FusedDeform.apply(self, x, t, *params)
+        # (grad mode is off inside autograd.Function.forward, so decide here whether to save activations)
+        need_grad = torch.is_grad_enabled() and (any(p.requires_grad for p in params) or x.requires_grad)
+        return _FusedDeform.apply(self, need_grad, x, t, *params)
 
 
 class DeformNetworkBaseline(_DeformBase):

@@ -195,6 +195,11 @@ int d3g_mlp_backward(const d3g_mlp_config* cfg, const void* packed, const d3g_ml
  * pipeline wait timed out, i.e. a bug).  Tests and debug mode call it; the hot path does not. */
 int d3g_mlp_read_status(const void* workspace, int32_t* status_host, void* stream);
 
+/* Parity / debug: activation pattern (relu'(z) bits) of trunk layer 0..7 saved by a forward with
+ * save_for_backward = 1.  dst_host[row*8 + c] bit j = (h_layer[row][c*32+j] > 0).  Synchronous. */
+int d3g_mlp_read_masks(const d3g_mlp_config* cfg, const void* workspace, int64_t rows, int32_t layer,
+                       uint32_t* dst_host, void* stream);
+
 /* tcgen05 self-test used by tests/: D[128,N] = A[128,K] * B[N,K]^T through the exact smem/TMEM
  * operand conventions the MLP kernels use.  mode 0: A,B K-major from smem; 1: A from TMEM;
  * 2: A,B MN-major from smem (A given as [K,128], B as [K,N]); 3: A MN-major, B = ones (N = 16), i.e.

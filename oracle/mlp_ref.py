@@ -90,11 +90,12 @@ class DeformRef:
         pe = np.concatenate([xe, tf], -1)
         c["pe"] = pe
         h = pe
-        c["in"], c["act"] = [], []
+        c["in"], c["act"], c["z"] = [], [], []
         for i in range(8):
             c["in"].append(h)
             z = h @ p["linear.%d.weight" % i].T + p["linear.%d.bias" % i]
             a = np.maximum(z, 0)
+            c["z"].append(z)
             c["act"].append(a)
             h = a
             if i == 4:
@@ -144,8 +145,11 @@ class DeformRef:
         g_w = g_w + g_theta * w_raw / theta
         return g_w, g_v
 
-    def backward(self, g_dxyz, g_rot=None, g_scale=None, want_input_grads=False):
-        """Returns a dict of parameter gradients (reference state_dict keys); optionally dL/dx, dL/dt."""
+    def backward(self, g_dxyz, g_rot=None, g_scale=None, want_input_grads=False, masks=None):
+        """Returns a dict of parameter gradients (reference state_dict keys); optionally dL/dx, dL/dt.
+        `masks` ([8,N,256] bool) overrides the ReLU activation pattern (z > 0) of the trunk, so that a
+        reduced-precision forward can be checked for arithmetic accuracy separately from the (inherent)
+        sign flips of pre-activations that sit within rounding noise of zero."""
         p, c, dt = self.p, self.cache, self.dtype
         grads = {}
         h = c["h"]
@@ -170,7 +174,7 @@ class DeformRef:
         g_pe = np.zeros_like(c["pe"])
         g = gh
         for i in range(7, -1, -1):
-            gz = g * (c["act"][i] > 0)
+            gz = g * ((c["act"][i] > 0) if masks is None else masks[i])
             g = lin_bwd("linear.%d" % i, c["in"][i], gz)
             if i == 5:
                 npe = c["pe"].shape[1]
