@@ -30,6 +30,22 @@ int set_err(int code, const char* fmt, ...);
                           cudaGetErrorString(_e), __FILE__, __LINE__);                       \
   } while (0)
 
+// ---- optional per-kernel timing (bench.py's roofline leg): CUDA events recorded on the launching stream
+// around every kernel of the path while d3g_prof_enable(1) is in force.  Off by default (zero cost).
+enum ProfId {
+  PROF_PREPROCESS_FWD = 0, PROF_SCAN, PROF_DUPLICATE, PROF_PAD_KEYS, PROF_SORT, PROF_RANGES, PROF_RENDER_FWD,
+  PROF_RENDER_BWD, PROF_PREPROCESS_BWD, PROF_MLP_TFEAT, PROF_MLP_FWD, PROF_MLP_DGRAD, PROF_MLP_WGRAD,
+  PROF_MLP_FINISH, PROF_MLP_PACK, PROF_COUNT
+};
+extern bool g_prof_on;
+void prof_begin(int id, cudaStream_t stream);
+void prof_end(int id, cudaStream_t stream);
+struct ProfScope {
+  int id; cudaStream_t s;
+  ProfScope(int id_, cudaStream_t s_) : id(id_), s(s_) { if (g_prof_on) prof_begin(id, s); }
+  ~ProfScope() { if (g_prof_on) prof_end(id, s); }
+};
+
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // ---- explicitly rounded float ops: never contracted, identical to the oracle's C expressions ----

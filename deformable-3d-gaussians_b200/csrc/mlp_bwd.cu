@@ -625,8 +625,9 @@ extern "C" int d3g_mlp_backward(const d3g_mlp_config* cfg, const void* packed, c
     size_t smem = BwdSmem::total + 1024;
     D3G_CUDA_TRY(cudaFuncSetAttribute(mlp_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = tiles < num_sms() ? tiles : num_sms();
+    { ProfScope _p(PROF_MLP_DGRAD, stream);
     mlp_dgrad_kernel<<<grid, kBwdThreads, smem, stream>>>(a);
-    D3G_LAUNCH_CHECK(0, stream);
+    D3G_LAUNCH_CHECK(0, stream); }
   }
   // ---- kernel 2: weight gradients ----
   {
@@ -663,8 +664,9 @@ extern "C" int d3g_mlp_backward(const d3g_mlp_config* cfg, const void* packed, c
     D3G_CUDA_TRY(cudaFuncSetAttribute(mlp_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = num_sms() & ~1;
     if (grid < 2) grid = 2;
+    { ProfScope _p(PROF_MLP_WGRAD, stream);
     mlp_wgrad_kernel<<<grid, kWgThreads, smem, stream>>>(a);
-    D3G_LAUNCH_CHECK(0, stream);
+    D3G_LAUNCH_CHECK(0, stream); }
     // ---- kernel 3 ----
     MlpFinishArgs f;
     memset(&f, 0, sizeof(f));
@@ -674,8 +676,9 @@ extern "C" int d3g_mlp_backward(const d3g_mlp_config* cfg, const void* packed, c
     f.db_fresh = db_fresh; f.w0 = p->linear_w[0]; f.w5 = p->linear_w[5]; f.pe_dim = pe_dim;
     f.t = t; f.thidden = ws.thidden; f.tn2_w = p->timenet2_w;
     f.g_tn0_w = g->timenet0_w; f.g_tn0_b = g->timenet0_b; f.g_tn2_w = g->timenet2_w; f.g_tn2_b = g->timenet2_b;
+    { ProfScope _p(PROF_MLP_FINISH, stream);
     mlp_finish_kernel<<<1, 256, 0, stream>>>(f);
-    D3G_LAUNCH_CHECK(0, stream);
+    D3G_LAUNCH_CHECK(0, stream); }
   }
   return 0;
 }

@@ -555,8 +555,9 @@ int d3g_mlp_pack_weights(const d3g_mlp_config* cfg, const d3g_mlp_params* p, voi
     return set_err(D3G_ERR_INVALID, "warp head parameters missing");
   cudaStream_t stream = (cudaStream_t)stream_;
   int total = (kFwdStages + kBwdStages) * 256 * 8 + kBiasFloats;
-  pack_weights_kernel<<<(total + 255) / 256, 256, 0, stream>>>(*cfg, *p, (uint8_t*)packed);
-  D3G_LAUNCH_CHECK(0, stream);
+  { ProfScope _p(PROF_MLP_PACK, stream);
+    pack_weights_kernel<<<(total + 255) / 256, 256, 0, stream>>>(*cfg, *p, (uint8_t*)packed);
+  D3G_LAUNCH_CHECK(0, stream); }
   return 0;
 }
 
@@ -574,10 +575,11 @@ int d3g_mlp_forward(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp
   D3G_CUDA_TRY(cudaMemsetAsync(ws.status, 0, 4, stream));
   if (rows == 0) return 0;
   int64_t rows_t = t_stride == 0 ? 1 : rows;
-  tfeat_kernel<<<(unsigned)rows_t, 256, 0, stream>>>(rows_t, t, t_stride, cfg->is_blender, p->timenet0_w,
+  { ProfScope _p(PROF_MLP_TFEAT, stream);
+    tfeat_kernel<<<(unsigned)rows_t, 256, 0, stream>>>(rows_t, t, t_stride, cfg->is_blender, p->timenet0_w,
                                                      p->timenet0_b, p->timenet2_w, p->timenet2_b, ws.tfeat,
                                                      save ? ws.thidden : nullptr);
-  D3G_LAUNCH_CHECK(0, stream);
+  D3G_LAUNCH_CHECK(0, stream); }
   MlpFwdArgs a;
   a.wfwd = (const uint8_t*)packed;
   a.bias = (const float*)((const uint8_t*)packed + kBiasOff);
@@ -591,8 +593,9 @@ int d3g_mlp_forward(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp
   size_t smem = FwdSmem::total + 1024;
   D3G_CUDA_TRY(cudaFuncSetAttribute(mlp_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = a.tiles < num_sms() ? a.tiles : num_sms();
-  mlp_fwd_kernel<<<grid, kFwdThreads, smem, stream>>>(a);
-  D3G_LAUNCH_CHECK(0, stream);
+  { ProfScope _p(PROF_MLP_FWD, stream);
+    mlp_fwd_kernel<<<grid, kFwdThreads, smem, stream>>>(a);
+  D3G_LAUNCH_CHECK(0, stream); }
   return 0;
 }
 

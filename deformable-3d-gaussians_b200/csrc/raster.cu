@@ -919,15 +919,20 @@ int d3g_raster_preprocess(const d3g_raster_settings* s, int32_t N, const float* 
   GeomView g = geom_view(geom, N);
   RasterArgs a = make_args(s, N, M);
   if (N > 0) {
+    { ProfScope _p(PROF_PREPROCESS_FWD, stream);
     preprocess_fwd_kernel<<<(N + 255) / 256, 256, 0, stream>>>(
         a, means3D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp, radii, g.means2D,
         g.conic_opacity, g.rgbd, g.cov3D, g.tiles_touched, g.clamped);
-    D3G_LAUNCH_CHECK(s->debug, stream);
+    D3G_LAUNCH_CHECK(s->debug, stream); }
     size_t tb = g.scan_temp_bytes;
+    ProfScope _p(PROF_SCAN, stream);
     D3G_CUDA_TRY(cub::DeviceScan::InclusiveSum(g.scan_temp, tb, g.tiles_touched, g.offsets, N, stream));
+    finish_scan_kernel<<<1, 1, 0, stream>>>(N, g.offsets, g.header);
+    D3G_LAUNCH_CHECK(s->debug, stream);
+  } else {
+    finish_scan_kernel<<<1, 1, 0, stream>>>(N, g.offsets, g.header);
+    D3G_LAUNCH_CHECK(s->debug, stream);
   }
-  finish_scan_kernel<<<1, 1, 0, stream>>>(N, g.offsets, g.header);
-  D3G_LAUNCH_CHECK(s->debug, stream);
   if (num_rendered_host)
     D3G_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, g.header, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
   return 0;
@@ -949,23 +954,28 @@ int d3g_raster_render(const d3g_raster_settings* s, int32_t N, uint64_t cap, voi
   if (tiles == 0) return 0;
   D3G_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, tiles * sizeof(uint2), stream));
   if (cap > 0 && N > 0) {
+    { ProfScope _p(PROF_DUPLICATE, stream);
     duplicate_with_keys_kernel<<<(N + 255) / 256, 256, 0, stream>>>(
         N, a.gx, a.gy, cap, g.means2D, g.rgbd, g.offsets, radii, b.keys_unsorted, b.vals_unsorted, g.header);
-    D3G_LAUNCH_CHECK(s->debug, stream);
+    D3G_LAUNCH_CHECK(s->debug, stream); }
+    { ProfScope _p(PROF_PAD_KEYS, stream);
     pad_keys_kernel<<<(unsigned)((cap + 255) / 256), 256, 0, stream>>>(cap, g.header, b.keys_unsorted, b.vals_unsorted);
-    D3G_LAUNCH_CHECK(s->debug, stream);
+    D3G_LAUNCH_CHECK(s->debug, stream); }
     size_t tb = b.sort_temp_bytes;
     int end_bit = 32 + bit_length((uint32_t)tiles);
-    D3G_CUDA_TRY(cub::DeviceRadixSort::SortPairs(b.sort_temp, tb, b.keys_unsorted, b.keys_sorted,
-                                                 b.vals_unsorted, b.point_list, (int)cap, 0, end_bit, stream));
+    { ProfScope _p(PROF_SORT, stream);
+      D3G_CUDA_TRY(cub::DeviceRadixSort::SortPairs(b.sort_temp, tb, b.keys_unsorted, b.keys_sorted,
+                                                   b.vals_unsorted, b.point_list, (int)cap, 0, end_bit, stream)); }
+    { ProfScope _p(PROF_RANGES, stream);
     identify_tile_ranges_kernel<<<(unsigned)((cap + 255) / 256), 256, 0, stream>>>(cap, g.header, b.keys_sorted, im.ranges);
-    D3G_LAUNCH_CHECK(s->debug, stream);
+    D3G_LAUNCH_CHECK(s->debug, stream); }
   }
   dim3 grid(a.gx, a.gy);
-  render_fwd_kernel<<<grid, kBlock, 0, stream>>>(a.H, a.W, a.gx, a.bg, im.ranges, b.point_list, g.means2D,
+  { ProfScope _p(PROF_RENDER_FWD, stream);
+    render_fwd_kernel<<<grid, kBlock, 0, stream>>>(a.H, a.W, a.gx, a.bg, im.ranges, b.point_list, g.means2D,
                                                  g.conic_opacity, g.rgbd, out_color, out_depth, im.final_T,
                                                  im.n_contrib);
-  D3G_LAUNCH_CHECK(s->debug, stream);
+  D3G_LAUNCH_CHECK(s->debug, stream); }
   return 0;
 }
 
@@ -992,16 +1002,18 @@ int d3g_raster_backward(const d3g_raster_settings* s, int32_t N, uint64_t cap, c
   D3G_CUDA_TRY(cudaMemsetAsync(g.acc_mean, 0, (size_t)((char*)g.scan_temp - (char*)g.acc_mean), stream));
   if ((size_t)a.gx * a.gy > 0) {
     dim3 grid(a.gx, a.gy);
+    { ProfScope _p(PROF_RENDER_BWD, stream);
     render_bwd_kernel<<<grid, kBlock, 0, stream>>>(a.H, a.W, a.gx, a.densify_mode, a.bg, im.ranges, b.point_list,
                                                    g.means2D, g.conic_opacity, g.rgbd, im.final_T, im.n_contrib,
                                                    dL_dcolor, dL_ddepth, g.acc_mean, g.acc_conic, g.acc_color);
-    D3G_LAUNCH_CHECK(s->debug, stream);
+    D3G_LAUNCH_CHECK(s->debug, stream); }
   }
-  preprocess_bwd_kernel<<<(N + 255) / 256, 256, 0, stream>>>(
+  { ProfScope _p(PROF_PREPROCESS_BWD, stream);
+    preprocess_bwd_kernel<<<(N + 255) / 256, 256, 0, stream>>>(
       a, means3D, shs, colors_precomp, scales, rotations, radii, g.cov3D, g.clamped, g.acc_mean, g.acc_conic,
       g.acc_color, dL_dmeans3D, dL_dmeans2D, dL_dmeans2D_densify, dL_dshs, dL_dcolors_precomp, dL_dopacities,
       dL_dscales, dL_drotations, dL_dcov3D_precomp);
-  D3G_LAUNCH_CHECK(s->debug, stream);
+  D3G_LAUNCH_CHECK(s->debug, stream); }
   return 0;
 }
 

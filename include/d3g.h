@@ -38,6 +38,15 @@ const char* d3g_last_error(void);
 /* ABI version, bumped on any signature change. */
 int d3g_version(void);
 
+/* Optional per-kernel timing for benchmarks: while enabled, CUDA events are recorded on the caller's
+ * stream around every kernel of the path.  d3g_prof_collect synchronises the device, adds up the
+ * elapsed time and the launch count per kernel id (arrays of at least d3g_prof_count() entries) and
+ * resets the recorder.  Process-global, not thread-safe; leave it off on the hot path. */
+int d3g_prof_enable(int32_t on);
+int d3g_prof_count(void);
+const char* d3g_prof_name(int32_t id);
+int d3g_prof_collect(double* total_ms, int32_t* launches, int32_t n);
+
 /* ------------------------------------------------------------------------------------------------
  * Rasterizer.  Replaces diff_gaussian_rasterization.{GaussianRasterizationSettings,GaussianRasterizer}
  * as constructed at gaussian_renderer/__init__.py:53-68 and invoked at :115-124 (returning image,
