@@ -11,10 +11,12 @@
 // Kernel 2 (mlp_wgrad_kernel) — dW_l = dZ_l^T * h_{l-1} is a GEMM whose K dimension is the points.
 //   Both operands are read as MN-major images straight from what forward / kernel 1 saved; CTA pairs
 //   split the 256 output features, the tile range is split-K over the pairs, partial sums leave TMEM
-//   through vector reductions (red.global.add.v4.f32) into the gradient tensors.  Bias gradients ride
-//   along as 16 extra accumulator columns (dZ^T * ones).
+//   through vector reductions (red.global.add.v4.f32) into the gradient tensors.  Bias gradients are
+//   column sums of the dZ stages taken by the otherwise idle epilogue warps (a 16-column ones-MMA was
+//   measured to cost as much tensor time as the 256-column one, tools/bench_umma.py).
 // Kernel 3 (mlp_finish_kernel) — head biases and the timenet (13->256->30) backward for a shared t.
 #include <math.h>
+#include <stdlib.h>
 
 #include "mlp_common.cuh"
 
@@ -331,7 +333,7 @@ struct WgItem {
   int N;                  // 256, 96 or 32
   int bias;               // accumulate dZ^T * ones into columns 256..271
   int kind;               // 0: trunk layer (dW[o][col0+i]), 1: heads (transposed scatter)
-  int cost;               // relative cost per tile
+  int cost;               // relative cost per tile: KB moved per 32-point stage (the kernel is HBM-bound)
   float* dW;              // trunk: gradient of linear.l.weight
   int ld, col0, ncols;
   float* db;              // trunk: gradient of linear.l.bias (or NULL)
@@ -339,6 +341,7 @@ struct WgItem {
 };
 
 struct MlpWgradArgs {
+  int dbg;                // bit0: skip the bulk loads, bit1: skip the MMAs (timing experiments only)
   WgItem items[kWgItems];
   int n_items;
   int tiles;
@@ -379,14 +382,12 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
   const int pair = blockIdx.x >> 1, pairs = gridDim.x >> 1, half = blockIdx.x & 1;
 
   if (tid == 0) {
-    for (int i = 0; i < kWgStages; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < kWgStages; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 5); }  // MMA commit + 4 warps
     mbar_init(acc_full, 1);
     mbar_init(acc_empty, 4);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, 512);
-  for (int i = tid; i < 512; i += kWgThreads) ((float*)sOnes)[i] = 1.0f;
-  fence_proxy_async();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -413,9 +414,12 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
           for (int ch = 0; ch < 4; ch++) {
             if (!mbar_wait(&empty[s], ph ^ 1, abort_flag)) { ok = false; break; }
             uint8_t* dst = sStage + (size_t)s * kWgStageBytes;
-            mbar_arrive_expect_tx(&full[s], kWgABytes + w.b_chunk_bytes);
-            bulk_g2s(dst, pa + (size_t)ch * 32768, kWgABytes, &full[s]);
-            bulk_g2s(dst + kWgABytes, pb + (size_t)ch * w.b_chunk_bytes, w.b_chunk_bytes, &full[s]);
+            if (a.dbg & 1) { mbar_arrive(&full[s]); }
+            else {
+              mbar_arrive_expect_tx(&full[s], kWgABytes + w.b_chunk_bytes);
+              bulk_g2s(dst, pa + (size_t)ch * 32768, kWgABytes, &full[s]);
+              bulk_g2s(dst + kWgABytes, pb + (size_t)ch * w.b_chunk_bytes, w.b_chunk_bytes, &full[s]);
+            }
             if (++s == kWgStages) { s = 0; ph ^= 1; }
           }
         }
@@ -428,8 +432,6 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
       uint32_t ph = 0, e_ph = 0;
       bool ok = true;
       int64_t base = 0;
-      const uint32_t idesc_ones = make_idesc_tf32(128, 16, 1, 0);
-      const uint64_t ones_desc = make_smem_desc(smem_u32(sOnes), 16, 1024);
       for (int it = 0; ok && it < a.n_items; it++) {
         const WgItem& w = a.items[it];
         int t0, t1;
@@ -448,12 +450,12 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
             const uint32_t sa = smem_u32(sStage + (size_t)s * kWgStageBytes), sb = sa + kWgABytes;
 #pragma unroll
             for (int k8 = 0; k8 < 4; k8++) {
+              if (a.dbg & 2) break;
               const uint64_t ad = make_smem_desc_mn(sa + k8 * 1024);
               umma_tf32_ss(tmem_base, ad, make_smem_desc_mn(sb + k8 * 1024), idesc, first ? 0u : 1u);
-              if (w.bias) umma_tf32_ss(tmem_base + 256, ad, ones_desc, idesc_ones, first ? 0u : 1u);
               first = 0;
             }
-            umma_commit(&empty[s]);
+            if (a.dbg & 8) mbar_arrive(&empty[s]); else umma_commit(&empty[s]);
             if (++s == kWgStages) { s = 0; ph ^= 1; }
           }
         }
@@ -468,12 +470,38 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
     uint32_t f_ph = 0;
     bool ok = true;
     int64_t base = 0;
+    int s = 0;
+    uint32_t ph = 0;
+    // bias gradients: thread f sums feature f of this CTA's half over the 32 points of every stage
+    // (CUDA cores; a 16-column "ones" MMA costs as much tensor time as the 256-column one)
+    const int f = (warp - 2) * 32 + lane;
+    const uint32_t f_off = (uint32_t)(f >> 5) * 4096u + (uint32_t)(f & 7) * 4u, f_chunk = (uint32_t)(f & 31) >> 3;
     for (int it = 0; ok && it < a.n_items; it++) {
       const WgItem& w = a.items[it];
       int t0, t1;
       wg_segment(a, pair, pairs, it, base, total, t0, t1);
       base += (int64_t)w.cost * a.tiles;
       if (t0 >= t1) continue;
+      float bsum = 0.f;
+      for (int tile = t0; ok && tile < t1; tile++) {
+        for (int ch = 0; ch < 4; ch++) {
+          if (!mbar_wait(&full[s], ph, abort_flag)) { ok = false; break; }
+          if (w.bias) {
+            const uint8_t* sa = sStage + (size_t)s * kWgStageBytes + f_off;
+            float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+            for (int p = 0; p < 32; p += 2) {
+              acc0 += *(const float*)(sa + p * 128 + ((f_chunk ^ (p & 3)) << 5));
+              acc1 += *(const float*)(sa + (p + 1) * 128 + ((f_chunk ^ ((p + 1) & 3)) << 5));
+            }
+            bsum += acc0 + acc1;
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&empty[s]);
+          if (++s == kWgStages) { s = 0; ph ^= 1; }
+        }
+      }
+      if (!ok) break;
       if (!mbar_wait(acc_full, f_ph, abort_flag)) { ok = false; break; }
       f_ph ^= 1;
       tc_fence_after();
@@ -481,6 +509,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
         uint32_t v[32];
         tmem_ld32(lane_addr + c0, v);
         tmem_wait_ld();
+        if (a.dbg & 4) continue;
         if (w.kind == 0) {
           float* dst = w.dW + (size_t)o * w.ld + w.col0 + c0;
 #pragma unroll
@@ -503,12 +532,9 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
         }
       }
       if (w.bias) {
-        uint32_t v[16];
-        tmem_ld16(lane_addr + 256, v);
-        tmem_wait_ld();
-        float g = __uint_as_float(v[0]);
-        if (w.db) atomicAdd(w.db + o, g);
-        if (w.db_fresh) atomicAdd(w.db_fresh + o, g);
+        const int ob = half * 128 + f;
+        if (w.db) atomicAdd(w.db + ob, bsum);
+        if (w.db_fresh) atomicAdd(w.db_fresh + ob, bsum);
       }
       tc_fence_before();
       __syncwarp();
@@ -633,6 +659,7 @@ extern "C" int d3g_mlp_backward(const d3g_mlp_config* cfg, const void* packed, c
   {
     MlpWgradArgs a;
     memset(&a, 0, sizeof(a));
+    { const char* e = getenv("D3G_WGRAD_DBG"); a.dbg = e ? atoi(e) : 0; }
     a.tiles = tiles; a.abort_flag = ws.status;
     const size_t layer_stride = (size_t)tiles * kHBytes;
     int n = 0;
@@ -646,14 +673,14 @@ extern "C" int d3g_mlp_backward(const d3g_mlp_config* cfg, const void* packed, c
       w.db_fresh = (bias && l == 0) ? db_fresh : ((bias && l == 5) ? db_fresh + 256 : nullptr);
     };
     for (int l = 7; l >= 1; l--)
-      trunk(l, ws.h_img + (size_t)(l - 1) * layer_stride, kHBytes, 256, 1, l == 5 ? pe_dim : 0, 256, 272);
-    trunk(0, ws.pe_img, kPeBytes, 96, 1, 0, pe_dim, 112);
-    trunk(5, ws.pe_img, kPeBytes, 96, 0, 0, pe_dim, 96);
+      trunk(l, ws.h_img + (size_t)(l - 1) * layer_stride, kHBytes, 256, 1, l == 5 ? pe_dim : 0, 256, 48);
+    trunk(0, ws.pe_img, kPeBytes, 96, 1, 0, pe_dim, 28);
+    trunk(5, ws.pe_img, kPeBytes, 96, 0, 0, pe_dim, 28);
     {
       WgItem& w = a.items[n++];
       w.a_img = ws.h_img + (size_t)7 * layer_stride;
       w.b_img = ws.dout_img; w.b_tile_bytes = kDoutBytes; w.b_chunk_bytes = 4096; w.N = 32;
-      w.bias = 0; w.kind = 1; w.cost = 32;
+      w.bias = 0; w.kind = 1; w.cost = 20;
     }
     a.n_items = n;
     d3g_mlp_params gp;  // the gradient struct has the same layout; reuse head_map on it

@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(128, 1)
 selftest_raw_kernel(const uint8_t* __restrict__ a_img, uint32_t a_bytes, const uint8_t* __restrict__ b_img,
                     uint32_t b_bytes, int n_mma, const uint64_t* __restrict__ adesc,
                     const uint64_t* __restrict__ bdesc, uint32_t idesc, int N, float* __restrict__ D,
-                    int* abort_flag) {
+                    int* abort_flag, int reps) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   __shared__ uint64_t bar;
@@ -177,14 +177,17 @@ selftest_raw_kernel(const uint8_t* __restrict__ a_img, uint32_t a_bytes, const u
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
   if (tid == 0) {
-    for (int i = 0; i < n_mma; i++) {
-      uint64_t ad = adesc[i] + (uint64_t)((smem_u32(sA) >> 4) & 0x3FFFu);
-      uint64_t bd = bdesc[i] + (uint64_t)((smem_u32(sB) >> 4) & 0x3FFFu);
-      umma_tf32_ss(tmem_base, ad, bd, idesc, i > 0);
-    }
+    for (int r = 0; r < reps; r++)
+      for (int i = 0; i < n_mma; i++) {
+        uint64_t ad = adesc[i] + (uint64_t)((smem_u32(sA) >> 4) & 0x3FFFu);
+        uint64_t bd = bdesc[i] + (uint64_t)((smem_u32(sB) >> 4) & 0x3FFFu);
+        umma_tf32_ss(tmem_base, ad, bd, idesc, (i | r) > 0);
+      }
     umma_commit(&bar);
   }
-  bool ok = mbar_wait(&bar, 0, abort_flag);
+  bool ok = false;
+  for (int w = 0; w < 64 && !ok && !*abort_flag; w++) { *abort_flag = 0; ok = mbar_wait(&bar, 0, abort_flag); }
+  if (ok) *abort_flag = 0;
   tc_fence_after();
   if (ok) {
     const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
@@ -205,7 +208,7 @@ selftest_raw_kernel(const uint8_t* __restrict__ a_img, uint32_t a_bytes, const u
 
 extern "C" int d3g_selftest_umma_raw(const void* a_img, uint32_t a_bytes, const void* b_img, uint32_t b_bytes,
                                      int32_t n_mma, const uint64_t* adesc, const uint64_t* bdesc, uint32_t idesc,
-                                     int32_t N, float* D, void* stream_) {
+                                     int32_t N, float* D, int32_t reps, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   if (a_bytes % 4 || b_bytes % 4 || a_bytes > 98304 || b_bytes > 98304 || N < 8 || N > 256 || n_mma < 1)
     return set_err(D3G_ERR_INVALID, "unsupported raw self-test arguments");
@@ -215,7 +218,7 @@ extern "C" int d3g_selftest_umma_raw(const void* a_img, uint32_t a_bytes, const 
   size_t smem = 1024 + 98304 + 98304 + 1024;
   D3G_CUDA_TRY(cudaFuncSetAttribute(selftest_raw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   selftest_raw_kernel<<<1, 128, smem, stream>>>((const uint8_t*)a_img, a_bytes, (const uint8_t*)b_img, b_bytes, n_mma,
-                                                adesc, bdesc, idesc, N, D, flag);
+                                                adesc, bdesc, idesc, N, D, flag, reps < 1 ? 1 : reps);
   cudaError_t e = cudaGetLastError();
   if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
   int h = 0;

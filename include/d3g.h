@@ -218,10 +218,10 @@ int d3g_selftest_umma(int32_t mode, int32_t N, int32_t K, const float* A, const 
 
 /* Raw tcgen05 probe (tests / tools only): host-supplied operand images, one shared-memory descriptor
  * pair per MMA (start-address field relative to the image), host-supplied instruction descriptor.
- * D is [128,N]. */
+ * D is [128,N].  The MMA list is issued `reps` times (reps > 1 is used to time instruction throughput). */
 int d3g_selftest_umma_raw(const void* a_img, uint32_t a_bytes, const void* b_img, uint32_t b_bytes,
                           int32_t n_mma, const uint64_t* adesc, const uint64_t* bdesc, uint32_t idesc,
-                          int32_t N, float* D, void* stream);
+                          int32_t N, float* D, int32_t reps, void* stream);
 
 #ifdef __cplusplus
 }

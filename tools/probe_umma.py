@@ -41,7 +41,7 @@ def run(a_img, b_img, ad, bd, idsc, N):
     adt = torch.tensor([ad], dtype=torch.int64).cuda()
     bdt = torch.tensor([bd], dtype=torch.int64).cuda()
     _lib.check(lib.d3g_selftest_umma_raw(_lib.ptr(a), a.numel() * 4, _lib.ptr(b), b.numel() * 4, 1, _lib.ptr(adt),
-                                         _lib.ptr(bdt), C.c_uint32(idsc), N, _lib.ptr(D), C.c_void_p(0)))
+                                         _lib.ptr(bdt), C.c_uint32(idsc), N, _lib.ptr(D), 1, C.c_void_p(0)))
     torch.cuda.synchronize()
     return D.cpu().numpy()
 
