@@ -140,13 +140,8 @@ class Workload:
         self.pipe = type("Pipe", (), dict(convert_SHs_python=False, compute_cov3D_python=False, debug=False))()
         # flat gradient buffer: parameter .grad tensors are views into it, so the multi-GPU exchange is
         # one all-reduce with no packing kernel
-        params = g.parameters() + list(self.model.deform.parameters())
-        self.params = params
-        self.flat = torch.zeros(sum(p.numel() for p in params), device=device)
-        o = 0
-        for p in params:
-            p.grad = self.flat[o:o + p.numel()].view_as(p)
-            o += p.numel()
+        self.grads = pkg("frames").FlatGrads(g.parameters() + list(self.model.deform.parameters()))
+        self.flat = self.grads.flat
         self.loss_host = torch.zeros(1).pin_memory()
         self.last = None
 

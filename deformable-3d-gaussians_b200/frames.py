@@ -1,0 +1,54 @@
+"""Frame-level data parallelism for the camera/time batch.
+
+The reference trains on `num_cams_per_iter` (camera, timestamp) frames per iteration in a serial Python
+loop on one GPU (train.py:224-247); frames are independent given the parameters, so they shard over
+ranks with ONE exchange step: the sum of the parameter gradients.  Parameters stay replicated.
+
+`FlatGrads` makes every parameter's `.grad` a view into one flat fp32 buffer, so that exchange is a single
+all-reduce with no packing kernel (NCCL over NVLink on the GPU box, gloo in the CPU tests).
+"""
+import torch
+
+
+def shard_frames(num_frames, world_size, rank):
+    """Frame k of the time-sorted batch goes to rank k mod G (train.py:148-154 sorts the batch in time)."""
+    return list(range(rank, num_frames, world_size))
+
+
+def frame_loss_weights(num_frames, lambda_dssim):
+    """Per-frame (L1 weight, SSIM weight) reproducing the reference's cumulative-Ll1 quirk
+    (train.py:245-250: `Ll1` accumulates across frames before entering the loss, then loss /= k)."""
+    T = num_frames
+    return [((T - j) * (1.0 - lambda_dssim) / T, lambda_dssim / T) for j in range(T)]
+
+
+class FlatGrads:
+    def __init__(self, params):
+        self.params = [p for p in params]
+        dev = self.params[0].device
+        self.flat = torch.zeros(sum(p.numel() for p in self.params), dtype=torch.float32, device=dev)
+        o = 0
+        for p in self.params:
+            p.grad = self.flat[o:o + p.numel()].view_as(p)
+            o += p.numel()
+
+    def zero(self):
+        self.flat.zero_()
+
+    def all_reduce(self, group=None):
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
+        return self.flat
+
+
+def reduce_densification_stats(grad_norm_accum, denom, max_radii2D, group=None):
+    """Densification statistics are per-frame quantities (scene/gaussian_model.py:398-401 takes the norm of
+    each frame's viewspace gradient BEFORE accumulating), so ranks reduce their local accumulators:
+    SUM for the gradient-norm accumulator and the visibility count, MAX for max_radii2D (train.py:238-239)."""
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(grad_norm_accum, op=dist.ReduceOp.SUM, group=group)
+        dist.all_reduce(denom, op=dist.ReduceOp.SUM, group=group)
+        dist.all_reduce(max_radii2D, op=dist.ReduceOp.MAX, group=group)
+    return grad_norm_accum, denom, max_radii2D
