@@ -518,19 +518,34 @@ render_fwd_kernel(int H, int W, int gx, const float* __restrict__ bg,
 }
 
 // ================================================================================================
-// stage 4: render backward (App. A.4).  Per (pixel,Gaussian) terms are reduced over the 32 pixels of a
-// warp with shuffles; lane 0 issues three 16-byte vector reductions (RED.128) per (warp,Gaussian)
-// instead of the ~10 scalar atomics per (pixel,Gaussian) of the classic kernel.
+// stage 4: render backward (App. A.4).  The twelve per-(pixel,Gaussian) gradient terms are reduced over
+// the 32 pixels of a warp with a 13-shuffle split butterfly (each step halves the number of live values
+// per lane instead of reducing every value five times), added into a per-batch shared-memory accumulator
+// shared by the 8 warps of the tile, and flushed once per (tile,Gaussian) with three 16-byte vector
+// reductions (RED.128) — instead of the ~10 scalar global atomics per (pixel,Gaussian) of the classic
+// kernel.  Backward is held to 1e-3 relative, not bit-exactness, so it uses MUFU ex2/rcp.
 // ================================================================================================
-__device__ __forceinline__ float warp_sum(float v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
 __device__ __forceinline__ void red_add_v4(float4* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
                : "memory");
 }
+__device__ __forceinline__ float fast_rcp(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float fast_ex2(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+// one butterfly step: lanes with `up` keep hi and send lo, the others keep lo and send hi
+__device__ __forceinline__ float bfly(float lo, float hi, bool up, int mask) {
+  float keep = up ? hi : lo, send = up ? lo : hi;
+  return keep + __shfl_xor_sync(0xffffffffu, send, mask);
+}
+
+static constexpr int kAccStride = 12;  // floats per Gaussian in the shared accumulator
 
 __global__ void __launch_bounds__(kBlock)
 render_bwd_kernel(int H, int W, int gx, int densify_mode, const float* __restrict__ bg,
@@ -542,104 +557,133 @@ render_bwd_kernel(int H, int W, int gx, int densify_mode, const float* __restric
                   float4* __restrict__ acc_conic, float4* __restrict__ acc_color) {
   __shared__ uint32_t s_id[kBlock];
   __shared__ float2 s_xy[kBlock];
-  __shared__ float4 s_co[kBlock];
+  __shared__ float4 s_co[kBlock];   // conic scaled by log2(e), opacity
   __shared__ float4 s_cd[kBlock];
-  int tile = blockIdx.y * gx + blockIdx.x;
-  int lx = threadIdx.x % kTile, ly = threadIdx.x / kTile;
-  int pxi = blockIdx.x * kTile + lx, pyi = blockIdx.y * kTile + ly;
-  bool inside = pxi < W && pyi < H;
-  float pfx = (float)pxi, pfy = (float)pyi;
-  uint2 range = ranges[tile];
+  __shared__ __align__(16) float s_acc[kBlock * kAccStride];
+  __shared__ int s_max[kBlock / 32];
+  const int tile = blockIdx.y * gx + blockIdx.x;
+  const int lane = threadIdx.x & 31;
+  const int lx = threadIdx.x % kTile, ly = threadIdx.x / kTile;
+  const int pxi = blockIdx.x * kTile + lx, pyi = blockIdx.y * kTile + ly;
+  const bool inside = pxi < W && pyi < H;
+  const float pfx = (float)pxi, pfy = (float)pyi;
+  const uint2 range = ranges[tile];
   int todo = (int)(range.y - range.x);
-  size_t P = (size_t)H * W;
-  size_t pix = inside ? (size_t)pyi * W + pxi : 0;
-  float T_final = inside ? final_T[pix] : 0.f;
+  const size_t P = (size_t)H * W;
+  const size_t pix = inside ? (size_t)pyi * W + pxi : 0;
+  const float T_final = inside ? final_T[pix] : 0.f;
   float T = T_final;
-  int last_contributor = inside ? (int)n_contrib[pix] : 0;
+  const int last_contributor = inside ? (int)n_contrib[pix] : 0;
   float dLp0 = 0.f, dLp1 = 0.f, dLp2 = 0.f, dLd = 0.f;
   if (inside) {
     dLp0 = dL_dpix[pix]; dLp1 = dL_dpix[P + pix]; dLp2 = dL_dpix[2 * P + pix];
     if (dL_ddepth) dLd = dL_ddepth[pix];
   }
-  float bg_dot = __ldg(bg) * dLp0 + __ldg(bg + 1) * dLp1 + __ldg(bg + 2) * dLp2;
+  const float bgT = -T_final * (__ldg(bg) * dLp0 + __ldg(bg + 1) * dLp1 + __ldg(bg + 2) * dLp2);
   float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, ard = 0.f;
   float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, ld = 0.f, last_alpha = 0.f;
-  float ddelx_dx = 0.5f * (float)W, ddely_dy = 0.5f * (float)H;
+  const float ddelx_dx = 0.5f * (float)W, ddely_dy = 0.5f * (float)H;
+  const float kLog2e = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
+  // butterfly bookkeeping: which of the 12 sums this lane ends up holding
+  const bool up16 = lane & 16, up8 = lane & 8, up4 = lane & 4, up2 = lane & 2;
+  const int my_slot = (up16 ? 6 : 0) + (up8 ? 3 : 0) + (up4 ? 2 : (up2 ? 1 : 0));
+  const bool slot_owner = !(lane & 1) && !(up4 && up2);
   // the block only needs the first max(last_contributor) entries of the list
-  int block_last = __reduce_max_sync(0xffffffffu, last_contributor);
   {
-    __shared__ int s_max[kBlock / 32];
-    if ((threadIdx.x & 31) == 0) s_max[threadIdx.x >> 5] = block_last;
+    int m = __reduce_max_sync(0xffffffffu, last_contributor);
+    if (lane == 0) s_max[threadIdx.x >> 5] = m;
     __syncthreads();
-    block_last = 0;
+    int block_last = 0;
 #pragma unroll
     for (int w = 0; w < kBlock / 32; w++) block_last = max(block_last, s_max[w]);
+    todo = min(todo, block_last);
   }
-  todo = min(todo, block_last);
   int contributor = todo;
   for (int base = 0; base < todo; base += kBlock) {
     __syncthreads();
-    int idx = base + threadIdx.x;
+    const int idx = base + threadIdx.x;
     if (idx < todo) {
       uint32_t id = point_list[range.x + (todo - 1 - idx)];
+      float4 co = conic_opacity[id];
       s_id[threadIdx.x] = id;
       s_xy[threadIdx.x] = means2D[id];
-      s_co[threadIdx.x] = conic_opacity[id];
+      s_co[threadIdx.x] = make_float4(co.x * kLog2e, co.y * kLog2e, co.z * kLog2e, co.w);
       s_cd[threadIdx.x] = rgbd[id];
     }
+    {
+      float4* z = (float4*)(s_acc + threadIdx.x * kAccStride);
+      z[0] = make_float4(0.f, 0.f, 0.f, 0.f); z[1] = z[0]; z[2] = z[0];
+    }
     __syncthreads();
-    int cnt = min(kBlock, todo - base);
+    const int cnt = min(kBlock, todo - base);
     for (int j = 0; j < cnt; j++) {
       contributor--;
-      bool valid = inside && contributor < last_contributor;
-      float2 xy = s_xy[j];
-      float4 co = s_co[j];
-      float dx = fs(xy.x, pfx), dy = fs(xy.y, pfy);
-      float q = ff(fm(co.z, dy), dy, fm(fm(co.x, dx), dx));
-      float power = ff(-0.5f, q, -fm(fm(co.y, dx), dy));
-      float G = det_exp(fminf(power, 0.0f));
-      float alpha = cmin(0.99f, fm(co.w, G));
-      valid = valid && !(power > 0.0f) && !(alpha < (float)(1.0 / 255.0));
-      unsigned any = __ballot_sync(0xffffffffu, valid);
-      if (any == 0u) continue;
-      float g_mx = 0.f, g_my = 0.f, g_dx = 0.f, g_dy = 0.f, g_cxx = 0.f, g_cxy = 0.f, g_cyy = 0.f,
-            g_op = 0.f, g_r = 0.f, g_g = 0.f, g_b = 0.f, g_z = 0.f;
+      const float2 xy = s_xy[j];
+      const float4 co = s_co[j];
+      const float dx = xy.x - pfx, dy = xy.y - pfy;
+      const float cdx = co.x * dx, cdy = co.z * dy;
+      const float p2 = -0.5f * (cdx * dx + cdy * dy) - co.y * dx * dy;  // power * log2(e)
+      const float G = fast_ex2(fminf(p2, 0.0f));
+      const float alpha = fminf(0.99f, co.w * G);
+      const bool valid = contributor < last_contributor && !(p2 > 0.0f) && !(alpha < (float)(1.0 / 255.0));
+      if (__ballot_sync(0xffffffffu, valid) == 0u) continue;
+      float v[12];
+#pragma unroll
+      for (int k = 0; k < 12; k++) v[k] = 0.f;
       if (valid) {
-        float4 cd = s_cd[j];
-        T = T / (1.0f - alpha);
-        float dch = alpha * T;
-        float dL_dalpha = 0.f;
+        const float4 cd = s_cd[j];
+        const float inv = fast_rcp(1.0f - alpha);
+        T *= inv;
+        const float dch = alpha * T;
         ar0 = last_alpha * lc0 + (1.0f - last_alpha) * ar0; lc0 = cd.x;
         ar1 = last_alpha * lc1 + (1.0f - last_alpha) * ar1; lc1 = cd.y;
         ar2 = last_alpha * lc2 + (1.0f - last_alpha) * ar2; lc2 = cd.z;
         ard = last_alpha * ld + (1.0f - last_alpha) * ard;  ld = cd.w;
-        dL_dalpha = (cd.x - ar0) * dLp0 + (cd.y - ar1) * dLp1 + (cd.z - ar2) * dLp2 + (cd.w - ard) * dLd;
-        g_r = dch * dLp0; g_g = dch * dLp1; g_b = dch * dLp2; g_z = dch * dLd;
-        dL_dalpha *= T;
+        float dL_dalpha = (cd.x - ar0) * dLp0 + (cd.y - ar1) * dLp1 + (cd.z - ar2) * dLp2 + (cd.w - ard) * dLd;
+        dL_dalpha = dL_dalpha * T + bgT * inv;
         last_alpha = alpha;
-        dL_dalpha += (-T_final / (1.0f - alpha)) * bg_dot;
-        float dL_dG = co.w * dL_dalpha;
-        float gdx = G * dx, gdy = G * dy;
-        float dG_ddelx = -gdx * co.x - gdy * co.y;
-        float dG_ddely = -gdy * co.z - gdx * co.y;
-        g_mx = dL_dG * dG_ddelx * ddelx_dx;
-        g_my = dL_dG * dG_ddely * ddely_dy;
-        if (densify_mode == 1) { g_dx = g_mx; g_dy = g_my; }
-        else if (densify_mode == 2) { g_dx = fabsf(g_mx); g_dy = fabsf(g_my); }
-        else { g_dx = sqrtf(g_mx * g_mx + g_my * g_my); g_dy = 0.f; }
-        g_cxx = -0.5f * gdx * dx * dL_dG;
-        g_cxy = -0.5f * gdx * dy * dL_dG;
-        g_cyy = -0.5f * gdy * dy * dL_dG;
-        g_op = G * dL_dalpha;
+        const float dL_dG = co.w * dL_dalpha;
+        const float gdx = G * dx, gdy = G * dy;
+        // s_co holds conic * log2(e): undo the scale once on the (conic . d) terms
+        const float cy_dx = co.y * dx, cy_dy = co.y * dy;
+        const float dG_ddelx = -kLn2 * (G * cdx + G * cy_dy);
+        const float dG_ddely = -kLn2 * (G * cdy + G * cy_dx);
+        const float g_mx = dL_dG * dG_ddelx * ddelx_dx;
+        const float g_my = dL_dG * dG_ddely * ddely_dy;
+        v[0] = g_mx; v[1] = g_my;
+        if (densify_mode == 1) { v[2] = g_mx; v[3] = g_my; }
+        else if (densify_mode == 2) { v[2] = fabsf(g_mx); v[3] = fabsf(g_my); }
+        else { v[2] = sqrtf(g_mx * g_mx + g_my * g_my); }
+        const float hG = -0.5f * dL_dG;
+        v[4] = hG * gdx * dx;
+        v[5] = hG * gdx * dy;
+        v[6] = hG * gdy * dy;
+        v[7] = G * dL_dalpha;
+        v[8] = dch * dLp0; v[9] = dch * dLp1; v[10] = dch * dLp2; v[11] = dch * dLd;
       }
-      g_mx = warp_sum(g_mx); g_my = warp_sum(g_my); g_dx = warp_sum(g_dx); g_dy = warp_sum(g_dy);
-      g_cxx = warp_sum(g_cxx); g_cxy = warp_sum(g_cxy); g_cyy = warp_sum(g_cyy); g_op = warp_sum(g_op);
-      g_r = warp_sum(g_r); g_g = warp_sum(g_g); g_b = warp_sum(g_b); g_z = warp_sum(g_z);
-      if ((threadIdx.x & 31) == 0) {
-        uint32_t id = s_id[j];
-        red_add_v4(acc_mean + id, g_mx, g_my, g_dx, g_dy);
-        red_add_v4(acc_conic + id, g_cxx, g_cxy, g_cyy, g_op);
-        red_add_v4(acc_color + id, g_r, g_g, g_b, g_z);
+      // split butterfly: 12 -> 6 -> 3 -> 2 -> 1 values per lane, 13 shuffles
+      float a6[6], b3[3];
+#pragma unroll
+      for (int k = 0; k < 6; k++) a6[k] = bfly(v[k], v[k + 6], up16, 16);
+#pragma unroll
+      for (int k = 0; k < 3; k++) b3[k] = bfly(a6[k], a6[k + 3], up8, 8);
+      const float c0 = bfly(b3[0], b3[2], up4, 4);
+      const float c1 = bfly(b3[1], 0.f, up4, 4);
+      float d = bfly(c0, c1, up2, 2);
+      d += __shfl_xor_sync(0xffffffffu, d, 1);
+      if (slot_owner) atomicAdd(s_acc + j * kAccStride + my_slot, d);
+    }
+    __syncthreads();
+    if (idx < todo) {
+      const float4* r = (const float4*)(s_acc + threadIdx.x * kAccStride);
+      const float4 m = r[0], c = r[1], k = r[2];
+      const bool nz = (m.x != 0.f) | (m.y != 0.f) | (m.z != 0.f) | (m.w != 0.f) | (c.x != 0.f) | (c.y != 0.f) |
+                      (c.z != 0.f) | (c.w != 0.f) | (k.x != 0.f) | (k.y != 0.f) | (k.z != 0.f) | (k.w != 0.f);
+      if (nz) {
+        const uint32_t id = s_id[threadIdx.x];
+        red_add_v4(acc_mean + id, m.x, m.y, m.z, m.w);
+        red_add_v4(acc_conic + id, c.x, c.y, c.z, c.w);
+        red_add_v4(acc_color + id, k.x, k.y, k.z, k.w);
       }
     }
   }
