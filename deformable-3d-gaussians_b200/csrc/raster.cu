@@ -463,7 +463,8 @@ render_fwd_kernel(int H, int W, int gx, const float* __restrict__ bg,
   __shared__ float4 s_co[kBlock];
   __shared__ float4 s_cd[kBlock];
   int tile = blockIdx.y * gx + blockIdx.x;
-  int lx = threadIdx.x % kTile, ly = threadIdx.x / kTile;
+  // a warp covers an 8x4 pixel block (compact footprint: fewer warps touched per splat than 16x2 strips)
+  int lx = (threadIdx.x & 7) | ((threadIdx.x >> 2) & 8), ly = ((threadIdx.x >> 3) & 3) | ((threadIdx.x >> 4) & 12);
   int pxi = blockIdx.x * kTile + lx, pyi = blockIdx.y * kTile + ly;
   bool inside = pxi < W && pyi < H;
   float pfx = (float)pxi, pfy = (float)pyi;
@@ -563,7 +564,7 @@ render_bwd_kernel(int H, int W, int gx, int densify_mode, const float* __restric
   __shared__ int s_max[kBlock / 32];
   const int tile = blockIdx.y * gx + blockIdx.x;
   const int lane = threadIdx.x & 31;
-  const int lx = threadIdx.x % kTile, ly = threadIdx.x / kTile;
+  const int lx = (threadIdx.x & 7) | ((threadIdx.x >> 2) & 8), ly = ((threadIdx.x >> 3) & 3) | ((threadIdx.x >> 4) & 12);
   const int pxi = blockIdx.x * kTile + lx, pyi = blockIdx.y * kTile + ly;
   const bool inside = pxi < W && pyi < H;
   const float pfx = (float)pxi, pfy = (float)pyi;
