@@ -142,6 +142,8 @@ class Workload:
         # one all-reduce with no packing kernel
         self.grads = pkg("frames").FlatGrads(g.parameters() + list(self.model.deform.parameters()))
         self.flat = self.grads.flat
+        # MLP backward adds straight into those .grad views (no per-parameter zero-fill + AccumulateGrad add)
+        self.model.deform.fused_grad_accumulation = True
         self.loss_host = torch.zeros(1).pin_memory()
         self.last = None
 

@@ -28,7 +28,8 @@ constexpr int kBwdThreads = 320;
 struct BwdSmem {
   static constexpr uint32_t dout = 0;                       // 16 KB K-major panel (32 columns)
   static constexpr uint32_t stages = kPanelBytes;
-  static constexpr uint32_t headb = stages + kBwdNumStages * kStageBytes;  // 16 floats
+  static constexpr uint32_t store = stages + kBwdNumStages * kStageBytes;  // 8 warps x 4 KB bulk-store staging
+  static constexpr uint32_t headb = store + 8 * 4096;                      // 16 floats
   static constexpr uint32_t bars = headb + 64;
   static constexpr uint32_t total = bars + 256;
 };
@@ -129,6 +130,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
   uint8_t* sDout = smem + BwdSmem::dout;
   uint8_t* sStage = smem + BwdSmem::stages;
   float* sHeadB = (float*)(smem + BwdSmem::headb);
+  uint8_t* sStore = smem + BwdSmem::store;
   uint64_t* bars = (uint64_t*)(smem + BwdSmem::bars);
   uint64_t* full = bars;                      // [kBwdNumStages]
   uint64_t* empty = bars + kBwdNumStages;     // [kBwdNumStages]
@@ -289,25 +291,39 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
           const uint32_t bits = mbits[i];
 #pragma unroll
           for (int k = 0; k < 32; k++) v[k] = ((bits >> k) & 1u) ? to_tf32(__uint_as_float(v[k])) : 0u;
-          if (j < 7) tmem_st32(lane_addr + half + c * 32, v);
-          uint8_t* dst = a.dz_img + ((size_t)l * a.tiles + tile) * kHBytes + (row >> 5) * 32768 + c * 4096 +
-                         (row & 31) * 128;
-#pragma unroll
-          for (int j8 = 0; j8 < 4; j8++) {
-            uint4* d4 = (uint4*)(dst + ((j8 ^ (row & 3)) << 5));
-            d4[0] = make_uint4(v[8 * j8], v[8 * j8 + 1], v[8 * j8 + 2], v[8 * j8 + 3]);
-            d4[1] = make_uint4(v[8 * j8 + 4], v[8 * j8 + 5], v[8 * j8 + 6], v[8 * j8 + 7]);
-          }
           if (j < 7) {
+            tmem_st32(lane_addr + half + c * 32, v);
             tmem_wait_st();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&a_ready[c]);
           }
+          // dZ block (32 rows x 128 B, contiguous in the wgrad image): staged in shared memory in the same
+          // swizzled layout and written by the bulk-copy engine as one 4 KB store
+          uint8_t* stg = sStore + (warp << 12);
+          if (lane == 0) bulk_wait_read<0>();
+          __syncwarp();
+          const bool swap = (lane >> 2) & 1;
+          uint8_t* line = stg + lane * 128 + (swap ? 16 : 0);
+#pragma unroll
+          for (int j8 = 0; j8 < 4; j8++) {
+            uint8_t* d = line + ((j8 ^ (lane & 3)) << 5);
+            const uint4 lo = make_uint4(v[8 * j8], v[8 * j8 + 1], v[8 * j8 + 2], v[8 * j8 + 3]);
+            const uint4 hi = make_uint4(v[8 * j8 + 4], v[8 * j8 + 5], v[8 * j8 + 6], v[8 * j8 + 7]);
+            *(uint4*)d = swap ? hi : lo;
+            *(uint4*)((uintptr_t)d ^ 16) = swap ? lo : hi;
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            bulk_s2g(a.dz_img + ((size_t)l * a.tiles + tile) * kHBytes + (size_t)q * 32768 + c * 4096, stg, 4096);
+            bulk_commit();
+          }
         }
       }
       tc_fence_before();
     }
+    if (lane == 0) bulk_wait_all<0>();
   }
   tc_fence_before();
   __syncthreads();

@@ -21,14 +21,15 @@
 
 namespace d3g {
 
-constexpr int kNumStages = 5;
+constexpr int kNumStages = 4;
 constexpr int kFwdThreads = 320;
 
 struct FwdSmem {
   // offsets inside dynamic shared memory (after 1024-alignment)
   static constexpr uint32_t pe = 0;
   static constexpr uint32_t stages = kPeBytes;
-  static constexpr uint32_t bias = stages + kNumStages * kStageBytes;
+  static constexpr uint32_t store = stages + kNumStages * kStageBytes;   // 8 warps x 4 KB bulk-store staging
+  static constexpr uint32_t bias = store + 8 * 4096;
   static constexpr uint32_t bars = bias + kBiasFloats * 4 + 64;  // 8-byte aligned
   static constexpr uint32_t total = bars + 256;
 };
@@ -65,6 +66,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
   uint8_t* sPE = smem + FwdSmem::pe;
   uint8_t* sStage = smem + FwdSmem::stages;
   float* sBias = (float*)(smem + FwdSmem::bias);
+  uint8_t* sStore = smem + FwdSmem::store;
   uint64_t* bars = (uint64_t*)(smem + FwdSmem::bars);
   uint64_t* full = bars;                   // [kNumStages]
   uint64_t* empty = bars + kNumStages;     // [kNumStages]
@@ -268,29 +270,50 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
           tmem_ld32(lane_addr + half + c * 32, v);
           tmem_wait_ld();
           uint32_t bits = 0;
+          float bv[32];
+#pragma unroll
+          for (int j = 0; j < 8; j++) {
+            const float4 b4 = ((const float4*)(bl + c * 32))[j];
+            bv[4 * j] = b4.x; bv[4 * j + 1] = b4.y; bv[4 * j + 2] = b4.z; bv[4 * j + 3] = b4.w;
+          }
 #pragma unroll
           for (int j = 0; j < 32; j++) {
-            float h = __uint_as_float(v[j]) + bl[c * 32 + j];
+            float h = __uint_as_float(v[j]) + bv[j];
             h = fmaxf(h, 0.f);
             bits |= (h > 0.f ? 1u : 0u) << j;
             v[j] = to_tf32(h);
           }
           tmem_st32(lane_addr + half + c * 32, v);
-          if (a.save) {
-            uint8_t* dst = a.h_img + ((size_t)l * a.tiles + tile) * kHBytes + (row >> 5) * 32768 + c * 4096 +
-                           (row & 31) * 128;
-#pragma unroll
-            for (int j8 = 0; j8 < 4; j8++) {
-              uint4* d4 = (uint4*)(dst + ((j8 ^ (row & 3)) << 5));
-              d4[0] = make_uint4(v[8 * j8], v[8 * j8 + 1], v[8 * j8 + 2], v[8 * j8 + 3]);
-              d4[1] = make_uint4(v[8 * j8 + 4], v[8 * j8 + 5], v[8 * j8 + 6], v[8 * j8 + 7]);
-            }
-            a.mask[(((size_t)l * a.tiles + tile) * 8 + c) * 128 + row] = bits;
-          }
+          // hand the chunk to the MMA warp first, then save it for backward
           tmem_wait_st();
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&a_ready[c]);
+          if (a.save) {
+            // The 32 rows x 128 B block this warp owns is contiguous in the wgrad image: build it in shared
+            // memory (same swizzled layout) and let the bulk-copy engine write it as one 4 KB store instead
+            // of 256 line-strided 16-byte stores per warp through L1.
+            uint8_t* stg = sStore + (warp << 12);
+            if (lane == 0) bulk_wait_read<0>();   // previous block has left the staging buffer
+            __syncwarp();
+            const bool swap = (lane >> 2) & 1;    // odd lane quads write the two 16 B halves in the other order
+            uint8_t* line = stg + lane * 128 + (swap ? 16 : 0);
+#pragma unroll
+            for (int j8 = 0; j8 < 4; j8++) {
+              uint8_t* d = line + ((j8 ^ (lane & 3)) << 5);
+              const uint4 lo = make_uint4(v[8 * j8], v[8 * j8 + 1], v[8 * j8 + 2], v[8 * j8 + 3]);
+              const uint4 hi = make_uint4(v[8 * j8 + 4], v[8 * j8 + 5], v[8 * j8 + 6], v[8 * j8 + 7]);
+              *(uint4*)d = swap ? hi : lo;
+              *(uint4*)((uintptr_t)d ^ 16) = swap ? lo : hi;
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+              bulk_s2g(a.h_img + ((size_t)l * a.tiles + tile) * kHBytes + (size_t)q * 32768 + c * 4096, stg, 4096);
+              bulk_commit();
+            }
+            a.mask[(((size_t)l * a.tiles + tile) * 8 + c) * 128 + row] = bits;
+          }
         }
       }
       if (!ok) break;
@@ -353,6 +376,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
       }
       tc_fence_before();
     }
+    if (lane == 0) bulk_wait_all<0>();
   }
   tc_fence_before();
   __syncthreads();

@@ -110,7 +110,30 @@ class _FusedDeform(torch.autograd.Function):
         f = lambda g: None if g is None else g.contiguous().float()
         g_xyz, g_rot, g_scale = f(g_xyz), f(g_rot), f(g_scale)
         named = _param_list(net)
-        grads = [torch.zeros_like(p, dtype=torch.float32) for _, p in named]
+        # The kernels only ever accumulate (red.global.add / +=) into the gradient buffers.  With
+        # net.fused_grad_accumulation set and every parameter already holding a contiguous fp32 .grad, they
+        # add straight into those tensors and autograd receives None (no zero-fill, no AccumulateGrad add
+        # per parameter).  Otherwise: one zero-filled flat buffer, returned as per-parameter views.
+        direct = net.fused_grad_accumulation and all(
+            p.grad is not None and p.grad.dtype == torch.float32 and p.grad.is_contiguous() and p.grad.device == dev
+            for _, p in named if p.requires_grad)
+        if direct:
+            scratch = None
+            grads = []
+            for _, p in named:
+                if p.requires_grad:
+                    grads.append(p.grad)
+                else:  # frozen parameter: its gradient goes to a scratch buffer nobody reads
+                    if scratch is None:
+                        scratch = torch.empty(max(q.numel() for _, q in named), dtype=torch.float32, device=dev)
+                    grads.append(scratch[:p.numel()].view_as(p))
+        else:
+            sizes = [(p.numel() + 3) // 4 * 4 for _, p in named]  # keep every view 16-byte aligned
+            flat = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
+            grads, off = [], 0
+            for (_, p), n in zip(named, sizes):
+                grads.append(flat[off:off + p.numel()].view_as(p))
+                off += n
         gstruct = _fill_ptr_struct(_lib.MlpGrads(), [(n, g) for (n, _), g in zip(named, grads)])
         pstruct = _fill_ptr_struct(_lib.MlpParams(), named)
         cfg = net._cfg()
@@ -132,7 +155,10 @@ class _FusedDeform(torch.autograd.Function):
             unused |= {"rot_w", "rot_b"}
         if not net._heads & HEAD_SCALE:
             unused |= {"scale_w", "scale_b"}
-        out = tuple(None if n in unused else g for (n, _), g in zip(named, grads))
+        if direct:
+            out = tuple(None for _ in named)
+        else:
+            out = tuple(None if n in unused else g for (n, _), g in zip(named, grads))
         return (None, None, dxyz_in, None) + out
 
 
@@ -169,6 +195,9 @@ class _DeformBase(nn.Module):
         self.gaussian_rotation = nn.Linear(W, 4)
         self.gaussian_scaling = nn.Linear(W, 3)
         self.debug = bool(int(os.environ.get("D3G_DEBUG", "0")))
+        # opt-in: backward adds into existing .grad tensors in place (see _FusedDeform.backward); only valid
+        # with loss.backward()-style accumulation, not with torch.autograd.grad()
+        self.fused_grad_accumulation = False
         self._pack_cache = None
 
     # -- C-ABI plumbing --------------------------------------------------------------------------

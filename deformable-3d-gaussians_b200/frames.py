@@ -26,11 +26,14 @@ class FlatGrads:
     def __init__(self, params):
         self.params = [p for p in params]
         dev = self.params[0].device
-        self.flat = torch.zeros(sum(p.numel() for p in self.params), dtype=torch.float32, device=dev)
+        # every view starts on a 16-byte boundary so the kernels' vector reductions (red.global.add.v4.f32)
+        # apply; the padding floats stay zero and ride along in the all-reduce
+        sizes = [(p.numel() + 3) // 4 * 4 for p in self.params]
+        self.flat = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
         o = 0
-        for p in self.params:
+        for p, n in zip(self.params, sizes):
             p.grad = self.flat[o:o + p.numel()].view_as(p)
-            o += p.numel()
+            o += n
 
     def zero(self):
         self.flat.zero_()
