@@ -165,3 +165,27 @@ def test_backward_large_vs_oracle():
      + (sc * torch.tensor(gs).cuda()).sum()).backward()
     ref = mlp_ref.DeformRef(params, dtype=np.float64)
     _check_backward(net, deform._FusedDeform.last_ws, N, ref, x, np.array([[0.5]]), gd, gr, gs, True)
+
+
+def test_fused_grad_accumulation_matches_autograd_accumulation():
+    """net.fused_grad_accumulation adds into existing .grad tensors in place; the result must equal what
+    autograd's AccumulateGrad produces from the returned gradients (two backward passes, summed)."""
+    params = mlp_ref.seeded_params(5)
+    rng = np.random.default_rng(11)
+    N = 3000
+    x = torch.tensor(rng.uniform(-1.3, 1.3, size=(N, 3)).astype(np.float32)).cuda()
+    t = torch.full((1, 1), 0.61).cuda().expand(N, 1)
+    cot = [torch.tensor(rng.standard_normal(s).astype(np.float32)).cuda() for s in ((N, 3), (N, 4), (N, 3))]
+    got = {}
+    for fused in (False, True):
+        net = _make_net(True, False, True, params)
+        net.fused_grad_accumulation = fused
+        for p in net.parameters():
+            p.grad = torch.zeros_like(p)
+        for _ in range(2):
+            outs = net(x, t)
+            sum((o * c).sum() for o, c in zip(outs, cot)).backward()
+        got[fused] = {k: p.grad.detach().cpu().numpy() for k, p in net.named_parameters()}
+    for k in got[False]:
+        # split-K partial sums land through atomics, so the two runs differ by fp32 summation order only
+        assert _rel(got[True][k], got[False][k]) < 1e-5, k
