@@ -4,11 +4,89 @@ Same signature, same branching (including the quirks listed in SURVEY.md §7: un
 `get_rotation + d_rotation`, deltas used verbatim under `direct_compute`, unreachable `override_color`)
 and the same returned dict.  The rasterizer behind it is this package's C-ABI one.
 """
+import ctypes as C
 import math
 
 import torch
 
+from . import _lib
 from .rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+
+# render() replaces the per-frame elementwise torch launches (parameter activations + deformation deltas)
+# by one fused kernel each way when `pc` exposes the reference GaussianModel's raw parameters and its
+# stock activation functions (scene/gaussian_model.py:58-78).  Set to False to force the torch-op path.
+FUSED_PREPARE = True
+
+
+class _PrepareGaussians(torch.autograd.Function):
+    """(xyz, d_xyz, _scaling, d_scaling, _rotation, d_rotation, _opacity) -> (means3D, opacity, scales,
+    rotations) exactly as gaussian_renderer/__init__.py:69-97 computes them, through d3g_gaussians_prepare."""
+
+    @staticmethod
+    def forward(ctx, xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity, is_6dof):
+        lib = _lib.load()
+        N = int(xyz.shape[0])
+        dev = xyz.device
+        new = lambda *shape: torch.empty(*shape, dtype=torch.float32, device=dev)
+        means3D, opac, scales, rots = new(N, 3), new(N, 1), new(N, 3), new(N, 4)
+        stream = torch.cuda.current_stream().cuda_stream
+        _lib.check(lib.d3g_gaussians_prepare(N, int(is_6dof), _lib.ptr(xyz), _lib.ptr(d_xyz), _lib.ptr(scaling),
+                                             _lib.ptr(d_scaling), _lib.ptr(rotation), _lib.ptr(d_rotation),
+                                             _lib.ptr(opacity), _lib.ptr(means3D), _lib.ptr(opac),
+                                             _lib.ptr(scales), _lib.ptr(rots), C.c_void_p(stream)))
+        ctx.is_6dof = bool(is_6dof)
+        ctx.save_for_backward(xyz, d_xyz, scaling, rotation, opacity)
+        ctx.set_materialize_grads(False)
+        return means3D, opac, scales, rots
+
+    @staticmethod
+    def backward(ctx, g_means, g_opac, g_scales, g_rots):
+        lib = _lib.load()
+        xyz, d_xyz, scaling, rotation, opacity = ctx.saved_tensors
+        N = int(xyz.shape[0])
+        dev = xyz.device
+        f = lambda g: None if g is None else g.contiguous().float()
+        g_means, g_opac, g_scales, g_rots = f(g_means), f(g_opac), f(g_scales), f(g_rots)
+        need = ctx.needs_input_grad
+        new = lambda *shape: torch.empty(*shape, dtype=torch.float32, device=dev)
+        six = ctx.is_6dof
+        g_xyz = new(N, 3) if (six and need[0]) else None
+        g_T = new(N, 4, 4) if (six and need[1]) else None
+        g_scaling = new(N, 3) if need[2] else None
+        g_rotation = new(N, 4) if need[4] else None
+        g_opacity = new(N, 1) if need[6] else None
+        stream = torch.cuda.current_stream().cuda_stream
+        _lib.check(lib.d3g_gaussians_prepare_backward(
+            N, int(six), _lib.ptr(xyz), _lib.ptr(d_xyz), _lib.ptr(scaling), _lib.ptr(rotation), _lib.ptr(opacity),
+            _lib.ptr(g_means), _lib.ptr(g_opac), _lib.ptr(g_scales), _lib.ptr(g_rots), _lib.ptr(g_xyz),
+            _lib.ptr(g_T), _lib.ptr(g_opacity), _lib.ptr(g_scaling), _lib.ptr(g_rotation), C.c_void_p(stream)))
+        if not six:  # additive: both operands receive the incoming cotangent itself
+            g_xyz = g_means if need[0] else None
+            g_T = g_means if need[1] else None
+        return (g_xyz, g_T, g_scaling, g_scales if need[3] else None, g_rotation, g_rots if need[5] else None,
+                g_opacity, None)
+
+
+def _can_fuse_prepare(pc, d_xyz, d_rotation, d_scaling, is_6dof):
+    if not FUSED_PREPARE:
+        return False
+    if not (torch.is_tensor(d_xyz) and torch.is_tensor(d_rotation) and torch.is_tensor(d_scaling)):
+        return False
+    if (getattr(pc, "scaling_activation", None) is not torch.exp
+            or getattr(pc, "opacity_activation", None) is not torch.sigmoid
+            or getattr(pc, "rotation_activation", None) is not torch.nn.functional.normalize):
+        return False
+    raw = [getattr(pc, n, None) for n in ("_xyz", "_scaling", "_rotation", "_opacity")]
+    if any(not torch.is_tensor(t) for t in raw):
+        return False
+    N = raw[0].shape[0]
+    shapes = [(N, 3), (N, 3), (N, 4), (N, 1)]
+    want_d = [(N, 4, 4) if is_6dof else (N, 3), (N, 4), (N, 3)]
+    tensors = raw + [d_xyz, d_rotation, d_scaling]
+    for t, shp in zip(tensors, shapes + want_d):
+        if tuple(t.shape) != shp or t.dtype != torch.float32 or not t.is_cuda or not t.is_contiguous():
+            return False
+    return True
 
 
 def eval_sh(deg, sh, dirs):
@@ -59,13 +137,10 @@ def _build_covariance(scaling, modifier, rotation):
 def render(viewpoint_camera, pc, pipe, bg_color, d_xyz, d_rotation, d_scaling, is_6dof=False,
            scaling_modifier=1.0, override_color=None, direct_compute=False):
     xyz = pc.get_xyz
-    screenspace_points = torch.zeros_like(xyz, dtype=xyz.dtype, requires_grad=True, device=xyz.device) + 0
-    screenspace_points_densify = torch.zeros_like(xyz, dtype=xyz.dtype, requires_grad=True, device=xyz.device) + 0
-    try:
-        screenspace_points.retain_grad()
-        screenspace_points_densify.retain_grad()
-    except Exception:
-        pass
+    # (the reference builds these as `zeros_like(...) + 0` and retains the gradient of the sum; leaf tensors
+    # behave identically for every consumer — .grad is populated by backward — without the two add launches)
+    screenspace_points = torch.zeros_like(xyz, dtype=xyz.dtype, requires_grad=True, device=xyz.device)
+    screenspace_points_densify = torch.zeros_like(xyz, dtype=xyz.dtype, requires_grad=True, device=xyz.device)
 
     tanfovx = math.tan(viewpoint_camera.FoVx * 0.5)
     tanfovy = math.tan(viewpoint_camera.FoVy * 0.5)
@@ -85,7 +160,12 @@ def render(viewpoint_camera, pc, pipe, bg_color, d_xyz, d_rotation, d_scaling, i
     )
     rasterizer = GaussianRasterizer(raster_settings=raster_settings)
 
-    if direct_compute:
+    fused = (not direct_compute and not getattr(pipe, "compute_cov3D_python", False)
+             and _can_fuse_prepare(pc, d_xyz, d_rotation, d_scaling, is_6dof))
+    if fused:
+        means3D, opacity, scales, rotations = _PrepareGaussians.apply(
+            pc._xyz, d_xyz, pc._scaling, d_scaling, pc._rotation, d_rotation, pc._opacity, bool(is_6dof))
+    elif direct_compute:
         means3D = d_xyz
     elif is_6dof:
         if torch.is_tensor(d_xyz) is False:
@@ -94,10 +174,13 @@ def render(viewpoint_camera, pc, pipe, bg_color, d_xyz, d_rotation, d_scaling, i
             means3D = _from_homogenous(torch.bmm(d_xyz, _to_homogenous(xyz).unsqueeze(-1)).squeeze(-1))
     else:
         means3D = xyz + d_xyz
-    opacity = pc.get_opacity
-
-    scales = rotations = cov3D_precomp = None
-    if getattr(pipe, "compute_cov3D_python", False):
+    cov3D_precomp = None
+    if not fused:
+        opacity = pc.get_opacity
+        scales = rotations = None
+    if fused:
+        pass  # scales / rotations / opacity came out of the fused kernel
+    elif getattr(pipe, "compute_cov3D_python", False):
         if hasattr(pc, "get_covariance"):
             cov3D_precomp = pc.get_covariance(scaling_modifier)
         else:

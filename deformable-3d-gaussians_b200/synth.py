@@ -100,6 +100,10 @@ class SynthGaussians:
         self._features_rest = (0.1 * torch.randn(N, M - 1, 3, generator=g)).to(device)
         self.active_sh_degree = sh_degree
         self.max_sh_degree = sh_degree
+        # GaussianModel.setup_functions, scene/gaussian_model.py:58-78
+        self.scaling_activation = torch.exp
+        self.opacity_activation = torch.sigmoid
+        self.rotation_activation = torch.nn.functional.normalize
 
     def parameters(self):
         return [self._xyz, self._features_dc, self._features_rest, self._opacity, self._scaling,
@@ -116,15 +120,15 @@ class SynthGaussians:
 
     @property
     def get_scaling(self):
-        return torch.exp(self._scaling)
+        return self.scaling_activation(self._scaling)
 
     @property
     def get_rotation(self):
-        return torch.nn.functional.normalize(self._rotation)
+        return self.rotation_activation(self._rotation)
 
     @property
     def get_opacity(self):
-        return torch.sigmoid(self._opacity)
+        return self.opacity_activation(self._opacity)
 
     @property
     def get_features(self):

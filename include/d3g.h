@@ -113,6 +113,26 @@ int d3g_raster_backward(const d3g_raster_settings* s, int32_t N, uint64_t pair_c
                         float* dL_dscales, float* dL_drotations, float* dL_dcov3D_precomp,
                         void* stream);
 
+/* Activation + deformation of the Gaussian parameters, fused (the elementwise work of
+ * gaussian_renderer/__init__.py:69-97 and of the getters of scene/gaussian_model.py:58-78):
+ *   means3D = xyz + d_xyz, or from_homogenous(d_xyz[N,4,4] . [xyz,1]) when is_6dof (utils/rigid_utils.py:86-107)
+ *   opacity_out = sigmoid(opacity); scales_out = exp(scaling) + d_scaling; rotations_out =
+ *   normalize(rotation) + d_rotation (d_scaling / d_rotation may be NULL = no delta).
+ * The backward call turns the cotangents of the four outputs (any may be NULL = zero) into the
+ * cotangents of the raw parameters (any output pointer may be NULL = not wanted); the cotangents of the
+ * additive deltas are the incoming cotangents themselves, g_dxyz_6dof [N,4,4] is written only when is_6dof,
+ * and g_xyz is written only when is_6dof (otherwise it equals g_means3D). */
+int d3g_gaussians_prepare(int32_t N, int32_t is_6dof, const float* xyz, const float* d_xyz,
+                          const float* scaling, const float* d_scaling, const float* rotation,
+                          const float* d_rotation, const float* opacity, float* means3D,
+                          float* opacity_out, float* scales_out, float* rotations_out, void* stream);
+int d3g_gaussians_prepare_backward(int32_t N, int32_t is_6dof, const float* xyz, const float* d_xyz,
+                                   const float* scaling, const float* rotation, const float* opacity,
+                                   const float* g_means3D, const float* g_opacity_out,
+                                   const float* g_scales_out, const float* g_rotations_out,
+                                   float* g_xyz, float* g_dxyz_6dof, float* g_opacity,
+                                   float* g_scaling, float* g_rotation, void* stream);
+
 /* Upstream `markVisible` (never called by the reference; provided for API completeness).
  * present[i] = 1 iff view-space z > 0.2. */
 int d3g_mark_visible(int32_t N, const float* means3D, const float* viewmatrix, uint8_t* present,

@@ -1,0 +1,144 @@
+"""GPU tests of the `render()` drop-in (gaussian_renderer/__init__.py:32-133): the fused activation+deformation
+kernel against the torch-op path it replaces, the 6-DoF branch, the reference's branching quirks, and
+DeformModel.step over several timestamps (scene/deform_model.py:260-273)."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import pkg
+from oracle import mlp_ref, raster_oracle as ro
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-30)
+
+
+def _scene(N, seed=5, H=96, W=128):
+    synth = pkg("synth")
+    dev = torch.device("cuda", 0)
+    g = synth.SynthGaussians(N, seed=seed, sh_degree=3)
+    for name in ("_xyz", "_features_dc", "_features_rest", "_opacity", "_scaling", "_rotation"):
+        setattr(g, name, getattr(g, name).to(dev).requires_grad_(True))
+    cam = synth.camera_to(synth.make_camera(W, H, theta_deg=40.0, fid=0.3), dev)
+    pipe = type("Pipe", (), dict(convert_SHs_python=False, compute_cov3D_python=False, debug=False))()
+    return g, cam, pipe, dev
+
+
+def _deltas(N, dev, is_6dof, seed=9):
+    gen = torch.Generator().manual_seed(seed)
+    if is_6dof:
+        T = torch.eye(4).repeat(N, 1, 1) + 0.02 * torch.randn(N, 4, 4, generator=gen)
+        T[:, 3, :3] = 0.01 * torch.randn(N, 3, generator=gen)
+        d_xyz = T
+    else:
+        d_xyz = 0.02 * torch.randn(N, 3, generator=gen)
+    d_rot = 0.05 * torch.randn(N, 4, generator=gen)
+    d_scale = 0.002 * torch.randn(N, 3, generator=gen).abs()
+    return [t.to(dev).requires_grad_(True) for t in (d_xyz, d_rot, d_scale)]
+
+
+def _run(g, cam, pipe, dev, deltas, is_6dof, fused):
+    renderer = pkg("renderer")
+    renderer.FUSED_PREPARE = fused
+    try:
+        for p in g.parameters() + deltas:
+            p.grad = None
+        out = renderer.render(cam, g, pipe, torch.zeros(3, device=dev), deltas[0], deltas[1], deltas[2], is_6dof)
+        cot = pkg("synth").image_cotangent(cam.image_height, cam.image_width).to(dev)
+        (out["render"] * cot).sum().backward()
+        torch.cuda.synchronize()
+    finally:
+        renderer.FUSED_PREPARE = True
+    grads = [p.grad.detach().cpu().numpy().copy() for p in g.parameters() + deltas]
+    return out, grads
+
+
+@pytest.mark.parametrize("is_6dof", [False, True])
+def test_fused_prepare_matches_torch_ops(is_6dof):
+    N = 4000
+    g, cam, pipe, dev = _scene(N)
+    deltas = _deltas(N, dev, is_6dof)
+    out_t, grads_t = _run(g, cam, pipe, dev, deltas, is_6dof, fused=False)
+    out_f, grads_f = _run(g, cam, pipe, dev, deltas, is_6dof, fused=True)
+    # same radii except where a 1-ulp difference in normalize() moves a ceil() boundary (none expected at N=4000)
+    assert (out_t["radii"] != out_f["radii"]).sum().item() <= 1
+    # bmm vs fused fma order moves 6-DoF means by an ulp: an alpha >= 1/255 test may flip at single pixels
+    dimg = (out_t["render"] - out_f["render"]).abs()
+    assert dimg.max().item() <= (5e-3 if is_6dof else 1e-5) and dimg.mean().item() <= 1e-6
+    assert (out_t["depth"] - out_f["depth"]).abs().max().item() <= (2e-2 if is_6dof else 1e-4)
+    names = ["xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation", "d_xyz", "d_rot", "d_scale"]
+    for n, a, b in zip(names, grads_f, grads_t):
+        assert _rel(a, b) < (1e-3 if is_6dof else 2e-4), n
+    assert out_f["viewspace_points"].grad is not None and out_f["viewspace_points_densify"].grad is not None
+    assert out_f["viewspace_points"].grad.shape == (N, 3)
+    assert torch.equal(out_f["visibility_filter"], out_f["radii"] > 0)
+
+
+def test_render_matches_oracle_through_public_api():
+    """render() on raw parameters + deltas against the CPU oracle fed with torch-CPU activations."""
+    N, H, W = 3000, 96, 128
+    g, cam, pipe, dev = _scene(N, H=H, W=W)
+    deltas = _deltas(N, dev, False)
+    out, grads = _run(g, cam, pipe, dev, deltas, False, fused=True)
+    synth = pkg("synth")
+    gc = synth.SynthGaussians(N, seed=5, sh_degree=3)
+    camc = synth.make_camera(W, H, theta_deg=40.0, fid=0.3)
+    d_xyz, d_rot, d_scale = [d.detach().cpu() for d in deltas]
+    cfg = ro.make_cfg(H, W, math.tan(camc.FoVx * 0.5), math.tan(camc.FoVy * 0.5), np.zeros(3), 1.0,
+                      camc.world_view_transform.numpy(), camc.full_proj_transform.numpy(),
+                      camc.camera_center.numpy(), 3, 16, 2, np.float32)
+    f = ro.forward(cfg, (gc.get_xyz + d_xyz).numpy(), gc.get_features.numpy(), None, gc.get_opacity.numpy(),
+                   (gc.get_scaling + d_scale).numpy(), (gc.get_rotation + d_rot).numpy(), None)
+    assert (out["radii"].cpu().numpy() != f["radii"]).sum() <= 1
+    assert np.abs(out["render"].detach().cpu().numpy() - f["color"]).max() <= 1e-4
+    assert np.abs(out["depth"].detach().cpu().numpy() - f["depth"]).max() <= 1e-4
+    go = ro.backward(cfg, f, synth.image_cotangent(H, W).numpy(), None)
+    assert _rel(grads[0], go["dL_dmeans3D"]) < 1e-3           # d(xyz) = d(means3D)
+    assert _rel(grads[6], go["dL_dmeans3D"]) < 1e-3           # d(d_xyz) likewise
+    assert _rel(grads[7], go["dL_drots"]) < 1e-3
+    assert _rel(grads[8], go["dL_dscales"]) < 1e-3
+    s = gc.get_opacity.numpy()
+    assert _rel(grads[3], go["dL_dopacity"].reshape(N, 1) * s * (1 - s)) < 1e-3
+    assert _rel(grads[4], go["dL_dscales"] * gc.get_scaling.numpy()) < 1e-3
+
+
+def test_render_branching_quirks():
+    """direct_compute uses the deltas verbatim; deltas of None use the plain getters (:83-97)."""
+    N = 1500
+    g, cam, pipe, dev = _scene(N)
+    renderer = pkg("renderer")
+    bg = torch.zeros(3, device=dev)
+    with torch.no_grad():
+        base = renderer.render(cam, g, pipe, bg, 0.0, None, None)
+        zero = renderer.render(cam, g, pipe, bg, torch.zeros(N, 3, device=dev), torch.zeros(N, 4, device=dev),
+                               torch.zeros(N, 3, device=dev))
+        direct = renderer.render(cam, g, pipe, bg, g.get_xyz, g.get_rotation, g.get_scaling, direct_compute=True)
+    assert (base["render"] - zero["render"]).abs().max().item() <= 1e-5
+    assert (base["render"] - direct["render"]).abs().max().item() <= 1e-5
+    assert set(base.keys()) == {"render", "viewspace_points", "viewspace_points_densify", "visibility_filter",
+                                "radii", "depth"}
+
+
+def test_deform_model_step_multi_timestamp():
+    """DeformModel.step loops over the columns of time_emb[N,T] and stacks d_xyz (scene/deform_model.py:260-273)."""
+    deform = pkg("deform")
+    params = mlp_ref.seeded_params(4, True, False)
+    model = deform.DeformModel(is_blender=True)
+    model.deform.load_state_dict({k: torch.tensor(v) for k, v in params.items()})
+    N, T = 2000, 3
+    rng = np.random.default_rng(2)
+    x = rng.uniform(-1.3, 1.3, size=(N, 3)).astype(np.float32)
+    times = np.array([0.1, 0.5, 0.9], np.float32)
+    time_emb = torch.tensor(times).cuda().unsqueeze(0).expand(N, T)
+    with torch.no_grad():
+        d_xyz, d_rot, d_scale = model.step(torch.tensor(x).cuda(), time_emb)
+    assert d_xyz.shape == (T, N, 3) and d_rot == [0, 0, 0] and d_scale == [0, 0, 0]
+    ref = mlp_ref.DeformRef(params, True, False, False, dtype=np.float64)
+    for k in range(T):
+        rd = ref.forward(x, np.array([[times[k]]]))[0]
+        assert _rel(d_xyz[k].cpu().numpy(), rd) < 1e-3
