@@ -145,6 +145,8 @@ class Workload:
         # MLP backward adds straight into those .grad views (no per-parameter zero-fill + AccumulateGrad add)
         self.model.deform.fused_grad_accumulation = True
         self.loss_host = torch.zeros(1).pin_memory()
+        self.copy_stream = torch.cuda.Stream(device=device)
+        self.gt_ready = torch.cuda.Event()
         self.last = None
 
     def frame(self, from_host):
@@ -158,12 +160,20 @@ class Workload:
             cam.full_proj_transform.copy_(self.host["proj"], non_blocking=True)
             cam.camera_center.copy_(self.host["campos"], non_blocking=True)
             cam.fid.copy_(self.host["fid"], non_blocking=True)
-            self.dev["gt"].copy_(self.host["gt"], non_blocking=True)
+            # the ground-truth image (7.7 MB) is only needed by the loss: upload it on a copy stream so the
+            # PCIe transfer overlaps the deformation MLP and the rasterizer of the same frame
+            main = torch.cuda.current_stream()
+            self.copy_stream.wait_stream(main)  # last frame's loss has finished reading the buffer
+            with torch.cuda.stream(self.copy_stream):
+                self.dev["gt"].copy_(self.host["gt"], non_blocking=True)
+                self.gt_ready.record(self.copy_stream)
         self.flat.zero_()
         N = g.get_xyz.shape[0]
         time_input = cam.fid.unsqueeze(0).expand(N, -1)
         d_xyz, d_rot, d_scale = self.model.step(g.get_xyz.detach(), time_input)
         out = render(cam, g, self.pipe, self.bg, d_xyz, d_rot, d_scale, self.cfg["is_6dof"])
+        if from_host:
+            torch.cuda.current_stream().wait_event(self.gt_ready)
         loss = (out["render"] - self.dev["gt"]).abs().mean()
         loss.backward()
         self.last = out
