@@ -140,7 +140,9 @@ class Workload:
         self.pipe = type("Pipe", (), dict(convert_SHs_python=False, compute_cov3D_python=False, debug=False))()
         # flat gradient buffer: parameter .grad tensors are views into it, so the multi-GPU exchange is
         # one all-reduce with no packing kernel
-        self.grads = pkg("frames").FlatGrads(g.parameters() + list(self.model.deform.parameters()))
+        # with several ranks the Gaussian slice is all-reduced while the MLP backward still runs
+        self.grads = pkg("frames").FlatGrads(g.parameters() + list(self.model.deform.parameters()),
+                                             early=len(g.parameters()) if world > 1 else 0)
         self.flat = self.grads.flat
         # MLP backward adds straight into those .grad views (no per-parameter zero-fill + AccumulateGrad add)
         self.model.deform.fused_grad_accumulation = True
@@ -195,7 +197,7 @@ def timed_region(work, steps, from_host, world, dist):
     for _ in range(steps):
         work.frame(from_host)
         if world > 1:
-            dist.all_reduce(work.flat)
+            work.grads.all_reduce()
     e1.record()
     torch.cuda.synchronize()
     sec = e0.elapsed_time(e1) / 1e3
@@ -218,6 +220,7 @@ def kernel_table(work, steps):
     lib.d3g_prof_enable(1)
     for _ in range(steps):
         work.frame(False)
+        work.grads.all_reduce()  # no-op on one rank
     ms = (C.c_double * n)()
     cnt = (C.c_int32 * n)()
     pkg("_lib").check(lib.d3g_prof_collect(ms, cnt, n))
@@ -367,7 +370,7 @@ def main():
     for _ in range(max(args.warmup, 3)):
         work.frame(False)
         if world > 1:
-            dist.all_reduce(work.flat)
+            work.grads.all_reduce()
     sampler = ClockSampler(local_rank)
     sampler.start()
     sec = timed_region(work, args.steps, False, world, dist)

@@ -23,7 +23,13 @@ def frame_loss_weights(num_frames, lambda_dssim):
 
 
 class FlatGrads:
-    def __init__(self, params):
+    """`params` in exchange order.  With `early` = the number of leading parameters whose gradients are
+    complete early in backward (the Gaussian parameters: autograd accumulates them right after the rasterizer
+    backward, before the deformation-MLP backward runs), `all_reduce()` becomes two collectives: the leading
+    slice is reduced asynchronously as soon as its last gradient has been accumulated — overlapping the MLP
+    backward kernels — and only the small trailing slice (the MLP gradients) is reduced at the end."""
+
+    def __init__(self, params, early=0):
         self.params = [p for p in params]
         dev = self.params[0].device
         # every view starts on a 16-byte boundary so the kernels' vector reductions (red.global.add.v4.f32)
@@ -31,17 +37,40 @@ class FlatGrads:
         sizes = [(p.numel() + 3) // 4 * 4 for p in self.params]
         self.flat = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
         o = 0
-        for p, n in zip(self.params, sizes):
+        self.early_len = 0
+        for i, (p, n) in enumerate(zip(self.params, sizes)):
             p.grad = self.flat[o:o + p.numel()].view_as(p)
             o += n
+            if i + 1 == early:
+                self.early_len = o
+        self._early_n, self._seen, self._work, self._group = int(early), 0, None, None
+        self.frames_per_reduce = 1  # local frames whose backward passes accumulate before one exchange
+        if early:
+            for p in self.params[:early]:
+                p.register_post_accumulate_grad_hook(self._on_grad)
+
+    def _on_grad(self, _p):
+        self._seen += 1
+        if self._seen == self._early_n * self.frames_per_reduce:
+            self._seen = 0
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized() and dist.get_world_size(self._group) > 1:
+                self._work = dist.all_reduce(self.flat[:self.early_len], op=dist.ReduceOp.SUM, group=self._group,
+                                             async_op=True)
 
     def zero(self):
         self.flat.zero_()
 
     def all_reduce(self, group=None):
+        """Sum the gradients over ranks (call after backward of this rank's last frame)."""
         import torch.distributed as dist
         if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
-            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
+            if self._work is not None:  # leading slice already in flight since mid-backward
+                dist.all_reduce(self.flat[self.early_len:], op=dist.ReduceOp.SUM, group=group)
+                self._work.wait()
+                self._work = None
+            else:
+                dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
         return self.flat
 
 

@@ -93,6 +93,7 @@ def _check_forward_bitexact(f, color, radii, depth, st):
     (3000, 160, 160, "blob", 3.0, 2),
     (777, 64, 48, "uniform", 6.0, 0),
     (50000, 400, 400, "blob", 1.0, 3),       # config C1
+    (100000, 800, 800, "uniform", 1.0, 3),   # config C2 at full size
 ])
 def test_forward_bit_exact(N, H, W, kind, scale_mul, deg):
     g, cam, bg = _scene(N, H, W, seed=N, kind=kind, scale_mul=scale_mul, sh_degree=deg)
@@ -206,3 +207,52 @@ def test_mark_visible():
     p = g.get_xyz.numpy()
     z = p[:, 0] * m[0, 2] + p[:, 1] * m[1, 2] + p[:, 2] * m[2, 2] + m[3, 2]
     assert np.mean(vis == (z > 0.2)) > 0.999
+
+
+@pytest.mark.parametrize("N,H,W", [(200000, 800, 800), (1000000, 1080, 1920)])  # C4 / C5 sizes
+def test_full_size_properties(N, H, W):
+    """Size-independent invariants at the sizes the oracle is too slow for: scan/duplication counts agree,
+    the sort is a stable-order permutation of the unsorted pairs (sortedness + checksum of checksums), tile
+    ranges partition the sorted list, per-pixel state is within bounds, and the path is deterministic."""
+    g, cam, bg = _scene(N, H, W, seed=7)
+    with torch.no_grad():
+        color, radii, depth, st, *_ = _gpu_forward(g, cam, bg, H, W)
+    R = st.R
+    tiles_touched = st.read(5, torch.int32, N).numpy().view(np.uint32).astype(np.int64)
+    offsets = st.read(6, torch.int32, N).numpy().view(np.uint32).astype(np.int64)
+    assert tiles_touched.sum() == R and offsets[-1] == R
+    assert np.array_equal(np.cumsum(tiles_touched), offsets)
+    assert np.array_equal(radii.cpu().numpy() > 0, tiles_touched > 0)
+    ku = st.read(13, torch.int64, R).numpy().view(np.uint64)
+    vu = st.read(14, torch.int32, R).numpy().view(np.uint32)
+    ks = st.read(8, torch.int64, R).numpy().view(np.uint64)
+    vs = st.read(9, torch.int32, R).numpy().view(np.uint32)
+    assert np.all(ks[1:] >= ks[:-1]), "sortedness"
+    # permutation: same multiset of (key, value) pairs — wrap-around sums of keys, values and a mixed hash
+    mix = lambda k, v: (k * np.uint64(0x9E3779B97F4A7C15)) ^ (v.astype(np.uint64) * np.uint64(0xC2B2AE3D27D4EB4F))
+    with np.errstate(over="ignore"):
+        assert ku.sum() == ks.sum() and vu.astype(np.uint64).sum() == vs.astype(np.uint64).sum()
+        assert mix(ku, vu).sum() == mix(ks, vs).sum(), "checksum of (key,value) pairs"
+    # the pair -> key map is intact: key of a sorted entry = (its tile, depth bits of its Gaussian)
+    depths = st.read(1, torch.float32, N).numpy().view(np.uint32)
+    assert np.array_equal((ks & np.uint64(0xFFFFFFFF)).astype(np.uint32), depths[vs])
+    # stability: equal keys keep the duplication order (ascending Gaussian index within equal (tile, depth))
+    same = ks[1:] == ks[:-1]
+    assert np.all(vs[1:][same] > vs[:-1][same])
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    ranges = st.read(10, torch.int32, 2 * T).numpy().view(np.uint32).reshape(T, 2).astype(np.int64)
+    tile_of = (ks >> np.uint64(32)).astype(np.int64)
+    counts = np.bincount(tile_of, minlength=T)
+    assert np.array_equal(ranges[:, 1] - ranges[:, 0], counts)
+    nz = counts > 0
+    assert np.array_equal(ranges[nz, 0], (np.cumsum(counts) - counts)[nz])
+    n_contrib = st.read(12, torch.int32, H * W).numpy().view(np.uint32).reshape(H, W)
+    final_T = st.read(11, torch.float32, H * W).numpy().reshape(H, W)
+    per_pixel_cap = np.repeat(np.repeat(counts.reshape((H + 15) // 16, (W + 15) // 16), 16, 0), 16, 1)[:H, :W]
+    assert np.all(n_contrib <= per_pixel_cap)
+    assert np.all((final_T >= 0) & (final_T <= 1)) and np.isfinite(color.cpu().numpy()).all()
+    # black background: image = sum of non-negative colours * weights; depth = sum of positive depths * weights
+    assert color.min().item() >= 0 and depth.min().item() >= 0
+    with torch.no_grad():
+        color2, radii2, depth2, *_ = _gpu_forward(g, cam, bg, H, W)
+    assert torch.equal(color, color2) and torch.equal(depth, depth2) and torch.equal(radii, radii2), "determinism"

@@ -142,3 +142,49 @@ def test_deform_model_step_multi_timestamp():
     for k in range(T):
         rd = ref.forward(x, np.array([[times[k]]]))[0]
         assert _rel(d_xyz[k].cpu().numpy(), rd) < 1e-3
+
+
+def test_pipeline_6dof_end_to_end():
+    """Config C4's path at reduced N: DeformNetworkBaseline(is_6dof) -> render(is_6dof=True) -> backward.
+    The image is checked against the oracle fed with the transformed means (numpy, from the GPU's own d_xyz);
+    the gradient reaching the se(3) head is checked against the torch-op path of render()."""
+    deform = pkg("deform")
+    synth = pkg("synth")
+    N, H, W = 3000, 96, 128
+    g, cam, pipe, dev = _scene(N, H=H, W=W)
+    params = mlp_ref.seeded_params(8, True, True, head_scale=0.01)
+    model = deform.DeformModelBaseline(is_blender=True, is_6dof=True)
+    model.deform.load_state_dict({k: torch.tensor(v) for k, v in params.items()})
+    t = cam.fid.unsqueeze(0).expand(N, -1)
+    grads = {}
+    for fused in (True, False):
+        pkg("renderer").FUSED_PREPARE = fused
+        try:
+            for p in list(model.deform.parameters()) + g.parameters():
+                p.grad = None
+            d_xyz, d_rot, d_scale = model.step(g.get_xyz.detach(), t)
+            assert d_xyz.shape == (N, 4, 4)
+            out = pkg("renderer").render(cam, g, pipe, torch.zeros(3, device=dev), d_xyz, d_rot, d_scale, True)
+            (out["render"] * synth.image_cotangent(H, W).to(dev)).sum().backward()
+            grads[fused] = {k: p.grad.detach().cpu().numpy().copy() for k, p in model.deform.named_parameters()
+                            if p.grad is not None}
+        finally:
+            pkg("renderer").FUSED_PREPARE = True
+    for k in ("branch_w.weight", "branch_v.weight", "linear.7.weight", "gaussian_rotation.weight"):
+        assert np.abs(grads[True][k]).max() > 0 and np.isfinite(grads[True][k]).all()
+        assert _rel(grads[True][k], grads[False][k]) < 2e-3, k
+    # image vs oracle on the GPU's own transform
+    Tm = d_xyz.detach().cpu().numpy().astype(np.float64)
+    xyz = g.get_xyz.detach().cpu().numpy().astype(np.float64)
+    hom = np.einsum("nij,nj->ni", Tm, np.concatenate([xyz, np.ones((N, 1))], 1))
+    means = (hom[:, :3] / hom[:, 3:]).astype(np.float32)
+    gc = synth.SynthGaussians(N, seed=5, sh_degree=3)
+    camc = synth.make_camera(W, H, theta_deg=40.0, fid=0.3)
+    cfg = ro.make_cfg(H, W, math.tan(camc.FoVx * 0.5), math.tan(camc.FoVy * 0.5), np.zeros(3), 1.0,
+                      camc.world_view_transform.numpy(), camc.full_proj_transform.numpy(),
+                      camc.camera_center.numpy(), 3, 16, 2, np.float32)
+    f = ro.forward(cfg, means, gc.get_features.numpy(), None, gc.get_opacity.numpy(),
+                   (gc.get_scaling + d_scale.detach().cpu()).numpy(), (gc.get_rotation + d_rot.detach().cpu()).numpy(), None)
+    diff = np.abs(out["render"].detach().cpu().numpy() - f["color"])
+    # fp32 vs fp64 evaluation of the transform moves means by an ulp: allow isolated 1/255-threshold flips
+    assert diff.mean() <= 1e-6 and diff.max() <= 5e-3

@@ -32,7 +32,10 @@ def _worker(rank, world, port, T, out):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     torch.manual_seed(0)
     params = [torch.randn(3, 2, requires_grad=True), torch.randn(2, requires_grad=True)]
-    fg = frames.FlatGrads(params)
+    # the first parameter plays the role of the Gaussian slice: reduced asynchronously from inside the last
+    # local frame's backward, the rest at the end
+    fg = frames.FlatGrads(params, early=1)
+    fg.frames_per_reduce = len(frames.shard_frames(T, world, rank))
     fg.zero()
     for k in frames.shard_frames(T, world, rank):
         _frame_loss(params, k).backward()
