@@ -233,8 +233,19 @@ def kernel_table(work, steps):
     return table, R
 
 
-def roofline(table, R, cfg, pk):
+def ncu_traffic(config_name):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of
+    this config (profiles/traffic_<config>.json, written by tools/summarize_ncu.py traffic); {} if none."""
+    path = os.path.join(ROOT, "profiles", "traffic_%s.json" % config_name)
+    if not os.path.exists(path):
+        return {}
+    with open(path) as f:
+        return json.load(f).get("kernels", {})
+
+
+def roofline(table, R, cfg, pk, traffic=None):
     """Algorithmic bytes / flops per launch over measured duration."""
+    traffic = traffic or {}
     N, P = cfg["N"], cfg["H"] * cfg["W"]
     Tl = ((cfg["W"] + 15) // 16) * ((cfg["H"] + 15) // 16)
     R = R or 0
@@ -260,6 +271,8 @@ def roofline(table, R, cfg, pk):
                              frac=ach / pk["bf16_tflops_sustained"], ms=ms, launches_per_step=per_step))
         else:
             rows.append(dict(kernel=name, bound=None, ms=ms, launches_per_step=per_step))
+    for r in rows:
+        r["traffic"] = traffic.get(r["kernel"])
     rows.sort(key=lambda r: -r["ms"] * r["launches_per_step"])
     return rows
 
@@ -396,13 +409,13 @@ def main():
 
     if not args.no_roofline:
         table, R = kernel_table(work, max(3, min(args.steps, 10)))
-        rows = roofline(table, R, cfg, peaks())
+        rows = roofline(table, R, cfg, peaks(), ncu_traffic(args.config))
         line["gpu_launches"] = int(round(sum(r["launches_per_step"] for r in rows) * args.steps))
         line["pairs_R"] = R
         top = next((r for r in rows if r.get("bound")), None)
         if top:
             line["roofline"] = {"kernel": top["kernel"], "bound": top["bound"], "achieved": top["achieved"],
-                                "peak": top["peak"], "unit": top["unit"], "frac": top["frac"], "traffic": None,
+                                "peak": top["peak"], "unit": top["unit"], "frac": top["frac"], "traffic": top["traffic"],
                                 "peak_source": peaks()["source"] + (" bf16 sustained; kind::tf32 runs at half that rate"
                                                                     if top["bound"] == "tensor" else " copy bandwidth")}
         line["kernels"] = [{k: (round(v, 5) if isinstance(v, float) else v) for k, v in r.items()} for r in rows]

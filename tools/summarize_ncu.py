@@ -51,6 +51,35 @@ def raw(path, out, title):
                     f.write("| %s | %s | %s |\n" % (w, r[i], units[i]))
 
 
-if __name__ == "__main__":
+def main():
     kind, path, out, title = sys.argv[1:5]
-    (launches if kind == "launches" else raw)(path, out, title)
+    {"launches": launches, "raw": raw, "traffic": traffic}[kind](path, out, title)
+
+
+def traffic(path, out, title):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of each of our kernels -> JSON read by bench.py
+    (the `traffic` key of the roofline object)."""
+    import json, re
+    rows = list(csv.reader(open(path)))
+    hdr, units = rows[0], rows[1]
+    ir, iw, ik = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum"), hdr.index("Kernel Name")
+    mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    names = {"render_fwd_kernel": "render_fwd", "render_bwd_kernel": "render_bwd", "mlp_fwd_kernel": "mlp_fwd",
+             "mlp_dgrad_kernel": "mlp_dgrad", "mlp_wgrad_kernel": "mlp_wgrad", "preprocess_fwd_kernel": "preprocess_fwd",
+             "preprocess_bwd_kernel": "preprocess_bwd", "duplicate_with_keys_kernel": "duplicate_with_keys",
+             "DeviceRadixSortOnesweepKernel": "radix_sort_pass"}
+    acc = {}
+    for r in rows[2:]:
+        for pat, short in names.items():
+            if re.search(pat, r[ik]):
+                b = float(r[ir].replace(",", "")) * mult[units[ir]] + float(r[iw].replace(",", "")) * mult[units[iw]]
+                acc.setdefault(short, []).append(b)
+    res = {"source": title, "unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)",
+           "kernels": {k: sum(v) / len(v) for k, v in acc.items()}}
+    if "radix_sort_pass" in res["kernels"]:
+        res["kernels"]["radix_sort"] = res["kernels"]["radix_sort_pass"] * 6  # 6 onesweep passes per sort at C2 (44 key bits)
+    json.dump(res, open(out, "w"), indent=1)
+
+
+if __name__ == "__main__":
+    main()
