@@ -228,3 +228,110 @@ extern "C" int d3g_selftest_umma_raw(const void* a_img, uint32_t a_bytes, const 
   if (h) return set_err(D3G_ERR_CUDA, "raw self-test: mbarrier wait timed out");
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Throughput probe for the MLP's inner step: `reps` x 4 MMAs (M=128, N=256, K=8, kind::tf32) issued by one
+// thread, timed with clock64 from first issue to commit arrival.
+//   mode 0: A from shared memory (SS)      mode 1: A from tensor memory (TS, as the trunk layers use it)
+//   mode 2: TS while warps 1..3 + 4..7 run the epilogue's tcgen05.ld/st pattern on the accumulator half
+//   mode 3: SS with the same interference
+//   mode 4: TS while eight warps spin on an mbarrier with all 32 lanes (what idle epilogue warps used to do)
+//   +8: tcgen05.commit after every 4 MMAs (as the weight ring does)   +16: non-zero operand data
+// Reports clocks per MMA per CTA (grid = any number of CTAs, one per SM).
+// ------------------------------------------------------------------------------------------------
+namespace d3g {
+__global__ void __launch_bounds__(288, 1)
+umma_clk_kernel(int mode_flags, int reps, long long* __restrict__ out, int* abort_flag) {
+  const int mode = mode_flags & 7;
+  const bool commit_each = mode_flags & 8, nonzero = mode_flags & 16;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_base_s;
+  __shared__ volatile int stop;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (warp == 8) tmem_alloc(&tmem_base_s, 512);
+  if (tid == 0) { mbar_init(&bar, 1); fence_barrier_init(); stop = 0; }
+  __shared__ uint64_t bar2;
+  if (tid == 0) mbar_init(&bar2, 1);
+  for (uint32_t i = tid; i < (65536u + 32768u) / 4; i += 288)
+    ((uint32_t*)smem)[i] = nonzero ? to_tf32(0.001f * (float)((i * 2654435761u) >> 20) - 2.0f) : 0u;
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+  if (nonzero && warp < 4) {
+    uint32_t v[32];
+#pragma unroll
+    for (int j = 0; j < 32; j++) v[j] = to_tf32(0.37f + 0.01f * j + 0.001f * lane);
+    for (int c = 0; c < 16; c++) tmem_st32(tmem_base + ((uint32_t)(warp * 32) << 16) + c * 32, v);
+    tmem_wait_st();
+    tc_fence_before();
+  }
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 8) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_tf32(128, 256, 0, 0);
+      const uint32_t sa = smem_u32(smem), sb = smem_u32(smem + 65536);
+      long long t0 = clock64();
+      for (int r = 0; r < reps; r++) {
+#pragma unroll
+        for (int ks = 0; ks < 4; ks++) {
+          if (mode & 1)
+            umma_tf32_ts(tmem_base, tmem_base + 256 + (r & 7) * 32 + ks * 8, make_smem_desc(sb + ks * 32, 16, 1024), idesc, 1u);
+          else
+            umma_tf32_ss(tmem_base, make_smem_desc(sa + ks * 32, 16, 1024), make_smem_desc(sb + ks * 32, 16, 1024), idesc, 1u);
+        }
+        if (commit_each) umma_commit(&bar2);
+      }
+      umma_commit(&bar);
+      mbar_wait(&bar, 0, abort_flag);
+      long long t1 = clock64();
+      out[blockIdx.x] = t1 - t0;
+      stop = 1;
+    }
+  } else if (mode == 4) {
+    // eight warps spinning on an mbarrier that never completes (what idle epilogue warps do)
+    __shared__ uint64_t never;
+    if (tid == 0) mbar_init(&never, 1);
+    __syncwarp();
+    while (!stop) mbar_try_wait(&never, 0);
+  } else if (mode >= 2) {
+    // epilogue-like traffic: 2 warps per lane quarter, ld 32 columns -> a few ALU ops -> st back, on columns 256..511
+    const uint32_t lane_addr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + 256;
+    int c = warp >> 2;
+    while (!stop) {
+      uint32_t v[32];
+      tmem_ld32(lane_addr + c * 32, v);
+      tmem_wait_ld();
+#pragma unroll
+      for (int j = 0; j < 32; j++) v[j] = to_tf32(fmaxf(__uint_as_float(v[j]) + 1.0f, 0.f));
+      tmem_st32(lane_addr + c * 32, v);
+      tmem_wait_st();
+      c = (c + 2) & 7;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) tmem_dealloc(tmem_base, 512);
+}
+}  // namespace d3g
+
+extern "C" int d3g_selftest_umma_clk(int32_t mode, int32_t reps, int32_t ctas, int64_t* clk_out, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (mode < 0 || mode > 31 || (mode & 7) > 4 || reps < 1 || ctas < 1 || ctas > 1024 || !clk_out)
+    return set_err(D3G_ERR_INVALID, "bad umma_clk arguments");
+  int* flag = nullptr;
+  D3G_CUDA_TRY(cudaMalloc(&flag, sizeof(int)));
+  D3G_CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(int), stream));
+  size_t smem = 1024 + 65536 + 32768;
+  D3G_CUDA_TRY(cudaFuncSetAttribute(umma_clk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  umma_clk_kernel<<<ctas, 288, smem, stream>>>(mode, reps, (long long*)clk_out, flag);
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+  cudaFree(flag);
+  if (e != cudaSuccess) return set_err(D3G_ERR_CUDA, "umma_clk failed: %s", cudaGetErrorString(e));
+  return 0;
+}

@@ -243,6 +243,11 @@ int d3g_selftest_umma_raw(const void* a_img, uint32_t a_bytes, const void* b_img
                           int32_t n_mma, const uint64_t* adesc, const uint64_t* bdesc, uint32_t idesc,
                           int32_t N, float* D, int32_t reps, void* stream);
 
+/* Throughput probe: `reps` x 4 MMAs (M=128, N=256, K=8, kind::tf32) per CTA on `ctas` CTAs; mode 0 = A from
+ * shared memory, 1 = A from tensor memory, 2/3 = the same with epilogue-like tcgen05.ld/st traffic from eight
+ * other warps, 4 = A from tensor memory while eight warps spin on an mbarrier.  clk_out (device, int64[ctas]) receives the clocks from first issue to commit arrival. */
+int d3g_selftest_umma_clk(int32_t mode, int32_t reps, int32_t ctas, int64_t* clk_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -37,3 +37,17 @@ timeit("SS MN-major N=96", [desc(4096, 512, 1, 1024 * k) for k in k4], [desc(409
 timeit("SS A MN / ones K N=16", [desc(4096, 512, 1, 1024 * k) for k in k4], [desc(16, 1024, 2, 0) for k in k4], idesc(128, 16, 1, 0), 16)
 timeit("SS K-major N=16", [desc(16, 1024, 2, 32 * k) for k in k4], [desc(16, 1024, 2, 32 * k) for k in k4], idesc(128, 16, 0, 0), 16)
 timeit("SS K-major N=128", [desc(16, 1024, 2, 32 * k) for k in k4], [desc(16, 1024, 2, 32 * k) for k in k4], idesc(128, 128, 0, 0), 128)
+
+# ---- in-kernel clocks per MMA: A from shared vs tensor memory, with/without epilogue-like TMEM traffic ----
+def clk(mode, ctas, reps=4000):
+    out = torch.zeros(ctas, dtype=torch.int64, device="cuda")
+    _lib.check(lib.d3g_selftest_umma_clk(mode, reps, ctas, _lib.ptr(out), C.c_void_p(0)))
+    torch.cuda.synchronize()
+    v = out.cpu().double() / (4 * reps)
+    return v.mean().item(), v.max().item()
+
+for ctas in (148,):
+    for mode, name in ((0, "SS"), (1, "TS"), (3, "SS + tcgen05.ld/st traffic"), (2, "TS + tcgen05.ld/st traffic"), (4, "TS + 8 warps polling mbarrier"), (1 + 8, "TS, commit every 4"), (1 + 16, "TS, non-zero data"), (1 + 8 + 16, "TS, commit every 4, non-zero data"), (2 + 8 + 16, "TS + ld/st traffic, commit/4, non-zero")):
+        clk(mode, ctas, 100)
+        m, mx = clk(mode, ctas)
+        print("%-28s ctas=%3d: %.1f clk/MMA mean, %.1f max" % (name, ctas, m, mx))
