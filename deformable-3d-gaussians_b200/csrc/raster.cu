@@ -459,6 +459,36 @@ __device__ __forceinline__ float reject_threshold(float opacity) {
   return -logf(255.0f * opacity) - 1e-4f;
 }
 
+// Which of the tile's eight warps (8x4 pixel blocks; warp w covers x-half w&1, y-quarter w>>1) can a Gaussian
+// reach?  {power >= thr} is the ellipse a*dx^2 + 2b*dx*dy + c*dy^2 <= -2*thr, whose bounding box has half
+// extents sqrt(-2*thr*c/det), sqrt(-2*thr*a/det).  The box is widened (0.1 % + 0.01 px) far beyond the fp32
+// rounding of `power`, so a warp whose bit is clear would have rejected the Gaussian at every pixel with the
+// exact per-pixel tests: skipping it leaves the results bit-identical.  Anything non-finite keeps all warps.
+__device__ __forceinline__ uint32_t warp_reach_mask(float mx, float my, float a, float b, float c, float thr,
+                                                    float tile_x0, float tile_y0) {
+  const float det = a * c - b * b;
+  const float inv = (-2.0f * thr) / det;
+  const float hx = sqrtf(c * inv) * 1.001f + 0.01f, hy = sqrtf(a * inv) * 1.001f + 0.01f;
+  if (!(det > 0.0f) || !(hx < 1e30f) || !(hy < 1e30f)) return 0xFFu;
+  const float x0 = mx - hx - tile_x0, x1 = mx + hx - tile_x0;
+  const float y0 = my - hy - tile_y0, y1 = my + hy - tile_y0;
+  const uint32_t xb = ((x1 >= 0.0f && x0 <= 7.0f) ? 1u : 0u) | ((x1 >= 8.0f && x0 <= 15.0f) ? 2u : 0u);
+  uint32_t m = 0;
+#pragma unroll
+  for (int q = 0; q < 4; q++)
+    if (y1 >= (float)(4 * q) && y0 <= (float)(4 * q + 3)) m |= xb << (2 * q);
+  return m;
+}
+// Transpose the per-Gaussian reach masks of a staged batch into one 256-bit bitmap per pixel warp.
+__device__ __forceinline__ void publish_reach(uint32_t m, uint32_t (*s_bits)[8]) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int p = 0; p < 8; p++) {
+    const uint32_t word = __ballot_sync(0xffffffffu, (m >> p) & 1u);
+    if (lane == p) s_bits[p][warp] = word;
+  }
+}
+
 // ================================================================================================
 // stage 3: render forward (App. A.3) — one CTA per 16x16 tile, one thread per pixel
 // ================================================================================================
@@ -472,6 +502,7 @@ render_fwd_kernel(int H, int W, int gx, const float* __restrict__ bg,
   __shared__ float4 s_xy[kBlock];   // (x, y, reject threshold on power, -)
   __shared__ float4 s_co[kBlock];
   __shared__ float4 s_cd[kBlock];
+  __shared__ uint32_t s_bits[8][8];   // [pixel warp][staging warp]: Gaussians of the batch that can reach the warp
   int tile = blockIdx.y * gx + blockIdx.x;
   // a warp covers an 8x4 pixel block (compact footprint: fewer warps touched per splat than 16x2 strips)
   int lx = (threadIdx.x & 7) | ((threadIdx.x >> 2) & 8), ly = ((threadIdx.x >> 3) & 3) | ((threadIdx.x >> 4) & 12);
@@ -486,18 +517,28 @@ render_fwd_kernel(int H, int W, int gx, const float* __restrict__ bg,
   for (int base = 0; base < todo; base += kBlock) {
     if (__syncthreads_count(done) == kBlock) break;
     int idx = base + threadIdx.x;
+    uint32_t reach = 0;
     if (idx < todo) {
       uint32_t id = point_list[range.x + idx];
       float2 m = means2D[id];
       float4 co = conic_opacity[id];
-      s_xy[threadIdx.x] = make_float4(m.x, m.y, reject_threshold(co.w), 0.f);
+      const float thr = reject_threshold(co.w);
+      s_xy[threadIdx.x] = make_float4(m.x, m.y, thr, 0.f);
       s_co[threadIdx.x] = co;
       s_cd[threadIdx.x] = rgbd[id];
+      reach = warp_reach_mask(m.x, m.y, co.x, co.y, co.z, thr, (float)(blockIdx.x * kTile), (float)(blockIdx.y * kTile));
     }
+    publish_reach(reach, s_bits);
     __syncthreads();
-    int cnt = min(kBlock, todo - base);
-    for (int j = 0; !done && j < cnt; j++) {
-      contributor++;
+    for (int wi = 0; wi < kBlock / 32; wi++) {
+      uint32_t word = s_bits[threadIdx.x >> 5][wi];
+      if (word == 0u) continue;
+      if (__all_sync(0xffffffffu, done)) break;
+      while (word) {
+      const int j = wi * 32 + __ffs(word) - 1;
+      word &= word - 1u;
+      if (done) continue;
+      contributor = (uint32_t)(base + j + 1);
       float4 xy = s_xy[j];
       float4 co = s_co[j];
       float dx = fs(xy.x, pfx), dy = fs(xy.y, pfy);
@@ -518,6 +559,7 @@ render_fwd_kernel(int H, int W, int gx, const float* __restrict__ bg,
       D = ff(cd.w, w, D);
       T = test_T;
       last = contributor;
+      }
     }
   }
   if (inside) {
@@ -576,6 +618,7 @@ render_bwd_kernel(int H, int W, int gx, int densify_mode, const float* __restric
   __shared__ float4 s_cd[kBlock];
   __shared__ __align__(16) float s_acc[kBlock * kAccStride];
   __shared__ int s_max[kBlock / 32];
+  __shared__ uint32_t s_bits[8][8];
   const int tile = blockIdx.y * gx + blockIdx.x;
   const int lane = threadIdx.x & 31;
   const int lx = (threadIdx.x & 7) | ((threadIdx.x >> 2) & 8), ly = ((threadIdx.x >> 3) & 3) | ((threadIdx.x >> 4) & 12);
@@ -614,26 +657,33 @@ render_bwd_kernel(int H, int W, int gx, int densify_mode, const float* __restric
     for (int w = 0; w < kBlock / 32; w++) block_last = max(block_last, s_max[w]);
     todo = min(todo, block_last);
   }
-  int contributor = todo;
   for (int base = 0; base < todo; base += kBlock) {
     __syncthreads();
     const int idx = base + threadIdx.x;
+    uint32_t reach = 0;
     if (idx < todo) {
       uint32_t id = point_list[range.x + (todo - 1 - idx)];
       float4 co = conic_opacity[id];
+      const float2 m = means2D[id];
       s_id[threadIdx.x] = id;
-      s_xy[threadIdx.x] = means2D[id];
+      s_xy[threadIdx.x] = m;
       s_co[threadIdx.x] = make_float4(co.x * kLog2e, co.y * kLog2e, co.z * kLog2e, co.w);
       s_cd[threadIdx.x] = rgbd[id];
+      reach = warp_reach_mask(m.x, m.y, co.x, co.y, co.z, reject_threshold(co.w), (float)(blockIdx.x * kTile),
+                              (float)(blockIdx.y * kTile));
     }
+    publish_reach(reach, s_bits);
     {
       float4* z = (float4*)(s_acc + threadIdx.x * kAccStride);
       z[0] = make_float4(0.f, 0.f, 0.f, 0.f); z[1] = z[0]; z[2] = z[0];
     }
     __syncthreads();
-    const int cnt = min(kBlock, todo - base);
-    for (int j = 0; j < cnt; j++) {
-      contributor--;
+    for (int wi = 0; wi < kBlock / 32; wi++) {
+      uint32_t word = s_bits[threadIdx.x >> 5][wi];
+      while (word) {
+      const int j = wi * 32 + __ffs(word) - 1;
+      word &= word - 1u;
+      const int contributor = todo - 1 - (base + j);
       const float2 xy = s_xy[j];
       const float4 co = s_co[j];
       const float dx = xy.x - pfx, dy = xy.y - pfy;
@@ -690,6 +740,7 @@ render_bwd_kernel(int H, int W, int gx, int densify_mode, const float* __restric
       float d = bfly(c0, c1, up2, 2);
       d += __shfl_xor_sync(0xffffffffu, d, 1);
       if (slot_owner) atomicAdd(s_acc + j * kAccStride + my_slot, d);
+      }
     }
     __syncthreads();
     if (idx < todo) {
