@@ -1149,6 +1149,12 @@ int d3g_raster_read_header(const void* geom, uint32_t header_host[2], void* stre
   return 0;
 }
 
+int d3g_raster_header_async(const void* geom, uint32_t* header_pinned, void* stream_) {
+  if (!geom || !header_pinned) return set_err(D3G_ERR_INVALID, "bad arguments");
+  D3G_CUDA_TRY(cudaMemcpyAsync(header_pinned, geom, 8, cudaMemcpyDeviceToHost, (cudaStream_t)stream_));
+  return 0;
+}
+
 int d3g_raster_read_state(int32_t which, int32_t N, int32_t H, int32_t W, uint64_t cap, const void* geom,
                           const void* bin, const void* img, void* dst, size_t dst_bytes, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;

@@ -39,6 +39,56 @@ DENSIFY_MODE = 2
 # binning workspace from it instead of reading the pair count back from the device.
 PAIR_CAPACITY_POLICY = None
 
+
+
+class GrowingPairCapacity:
+    """Sync-free capacity policy for PAIR_CAPACITY_POLICY.  The first frame of a shape reads the pair count R back
+    like the reference does (`num_rendered`); later frames size the binning workspace from the largest R seen so
+    far times `headroom` and only enqueue an asynchronous copy of the device header {R, overflow}.  `check()`
+    (call it wherever the host synchronises anyway, e.g. after reading the loss) raises if a frame overflowed
+    its capacity — the library flags that frame's image as undefined — and grows the capacity for the next one."""
+
+    def __init__(self, headroom=1.25):
+        self.headroom, self.seen, self.pending, self.free = float(headroom), {}, [], []
+
+    def __call__(self, N, H, W):
+        self._drain(block=False)
+        r = self.seen.get((N, H, W))
+        return None if r is None else int(r * self.headroom) + 1024
+
+    def observe(self, key, cap, geom, lib):
+        host = self.free.pop() if self.free else torch.zeros(2, dtype=torch.int32).pin_memory()
+        stream = torch.cuda.current_stream()
+        _lib.check(lib.d3g_raster_header_async(_lib.ptr(geom), C.c_void_p(host.data_ptr()), C.c_void_p(stream.cuda_stream)))
+        ev = torch.cuda.Event()
+        ev.record(stream)
+        self.pending.append((key, cap, host, ev, geom))
+
+    def record_exact(self, key, R):
+        self.seen[key] = max(self.seen.get(key, 0), R)
+
+    def _drain(self, block):
+        overflowed = None
+        while self.pending:
+            key, cap, host, ev, _geom = self.pending[0]
+            if not block and not ev.query():
+                break
+            ev.synchronize()
+            self.pending.pop(0)
+            self.free.append(host)
+            R = int(host[0].item()) & 0xFFFFFFFF
+            self.seen[key] = max(self.seen.get(key, 0), R)
+            if int(host[1].item()) != 0 or R > cap:
+                overflowed = (key, cap, R)
+        return overflowed
+
+    def check(self):
+        bad = self._drain(block=True)
+        if bad is not None:
+            raise RuntimeError("GaussianRasterizer: %d pairs exceeded the capacity %d of a sync-free frame (N,H,W=%s); "
+                               "that frame's image is undefined — re-render it" % (bad[2], bad[1], bad[0]))
+
+
 _pinned = {}
 
 
@@ -122,19 +172,27 @@ def rasterize_forward(rs, means3D, shs, colors_precomp, opacities, scales, rotat
                                          _lib.ptr(rotations), _lib.ptr(cov3D_precomp), _lib.ptr(geom),
                                          _lib.ptr(radii), C.c_void_p(0 if host is None else host.data_ptr()),
                                          C.c_void_p(stream)))
-    if policy is None:
+    cap = None if policy is None else policy(N, H, W)
+    if cap is None:
+        if host is None:
+            host = _pinned_u32(dev)
+            _lib.check(lib.d3g_raster_header_async(_lib.ptr(geom), C.c_void_p(host.data_ptr()), C.c_void_p(stream)))
         torch.cuda.current_stream().synchronize()
         R = int(host[0].item()) & 0xFFFFFFFF
         cap = R
+        if hasattr(policy, "record_exact"):
+            policy.record_exact((N, H, W), R)
     else:
         R = None
-        cap = int(policy(N, H, W))
+        cap = int(cap)
     bb = C.c_size_t()
     _lib.check(lib.d3g_raster_bin_bytes(C.c_uint64(cap), C.byref(bb)))
     binb = torch.empty(bb.value, dtype=torch.uint8, device=dev)
     _lib.check(lib.d3g_raster_render(C.byref(s), N, C.c_uint64(cap), _lib.ptr(geom), _lib.ptr(binb),
                                      _lib.ptr(img), _lib.ptr(radii), _lib.ptr(color), _lib.ptr(depth),
                                      C.c_void_p(stream)))
+    if R is None and hasattr(policy, "observe"):
+        policy.observe((N, H, W), cap, geom, lib)   # {R, overflow} of this frame, checked off the critical path
     return color, radii, depth, RasterState(N, H, W, cap, geom, binb, img, R)
 
 

@@ -145,6 +145,9 @@ int d3g_mark_visible(int32_t N, const float* means3D, const float* viewmatrix, u
  *        12 n_contrib[H*W] u32 | 13 unsorted keys[R] u64 | 14 unsorted values[R] u32
  * header_host receives {R, overflow}. */
 int d3g_raster_read_header(const void* geom, uint32_t header_host[2], void* stream);
+/* Same copy of {R, overflow}, enqueued on `stream` without synchronising (header_pinned must be pinned host
+ * memory): lets a caller that sized pair_capacity ahead of time verify it later, off the critical path. */
+int d3g_raster_header_async(const void* geom, uint32_t* header_pinned, void* stream);
 int d3g_raster_read_state(int32_t which, int32_t N, int32_t H, int32_t W, uint64_t pair_capacity,
                           const void* geom, const void* bin, const void* img, void* dst_host,
                           size_t dst_bytes, void* stream);

@@ -256,3 +256,44 @@ def test_full_size_properties(N, H, W):
     with torch.no_grad():
         color2, radii2, depth2, *_ = _gpu_forward(g, cam, bg, H, W)
     assert torch.equal(color, color2) and torch.equal(depth, depth2) and torch.equal(radii, radii2), "determinism"
+
+
+@pytest.mark.gpu
+def test_growing_pair_capacity_is_sync_free_and_identical():
+    """Frames rendered with a capacity sized ahead of time (no num_rendered read-back) equal the default path
+    bit for bit, and an undersized capacity is reported by check()."""
+    import importlib
+    ras = importlib.import_module("deformable-3d-gaussians_b200.rasterizer")
+    synth = importlib.import_module("deformable-3d-gaussians_b200.synth")
+    dev = torch.device("cuda", 0)
+    N, H, W = 20000, 256, 256
+    g = synth.SynthGaussians(N, seed=5, sh_degree=3)
+    cam = synth.camera_to(synth.make_camera(W, H, theta_deg=10.0, fid=0.5), dev)
+    rs = ras.GaussianRasterizationSettings(
+        image_height=H, image_width=W, tanfovx=math.tan(cam.FoVx * 0.5), tanfovy=math.tan(cam.FoVy * 0.5),
+        bg=torch.zeros(3, device=dev), scale_modifier=1.0, viewmatrix=cam.world_view_transform,
+        projmatrix=cam.full_proj_transform, sh_degree=3, campos=cam.camera_center, prefiltered=False, debug=False)
+    args = [t.to(dev) for t in (g.get_xyz, g.get_features, g.get_opacity, g.get_scaling, g.get_rotation)]
+
+    def frame():
+        return ras.rasterize_forward(rs, args[0], args[1], None, args[2], args[3], args[4], None)
+
+    assert ras.PAIR_CAPACITY_POLICY is None
+    c0, r0, d0, st0 = frame()
+    pol = ras.GrowingPairCapacity(1.25)
+    ras.PAIR_CAPACITY_POLICY = pol
+    try:
+        c1, _, _, st1 = frame()                 # first frame of a shape: exact read-back
+        assert st1.R == st0.R and st1.cap == st0.R
+        c2, r2, d2, st2 = frame()               # later frames: capacity from the policy, no read-back
+        assert st2.R is None and st2.cap > st0.R
+        pol.check()
+        assert torch.equal(c2, c0) and torch.equal(r2, r0) and torch.equal(d2, d0)
+        pol.seen[(N, H, W)] = st0.R // 4        # force an undersized capacity
+        pol.headroom = 1.0
+        frame()
+        with pytest.raises(RuntimeError):
+            pol.check()
+        assert pol.seen[(N, H, W)] == st0.R     # grown from the observed count
+    finally:
+        ras.PAIR_CAPACITY_POLICY = None
