@@ -133,6 +133,15 @@ int d3g_gaussians_prepare_backward(int32_t N, int32_t is_6dof, const float* xyz,
                                    float* g_xyz, float* g_dxyz_6dof, float* g_opacity,
                                    float* g_scaling, float* g_rotation, void* stream);
 
+/* Fused image loss of the training step (utils/loss_utils.py:18-19 l1_loss, :42-73 ssim with its 11x11 sigma-1.5
+ * window, zero padding and C1/C2; combined as in train_baseline.py:126-127).  img, gt: [C,H,W] fp32 device.
+ * out3 (device float[3]) receives {mean|img-gt|, mean SSIM, w_l1*L1 + w_ssim*SSIM + bias}; the reference's loss
+ * is w_l1 = 1-lambda, w_ssim = -lambda, bias = lambda.  dL_dimg (nullable, [C,H,W]) receives the gradient of
+ * out3[2] w.r.t. img.  workspace: d3g_image_loss_workspace_bytes(C,H,W) bytes of device memory. */
+int d3g_image_loss_workspace_bytes(int32_t C, int32_t H, int32_t W, size_t* bytes);
+int d3g_image_loss(int32_t C, int32_t H, int32_t W, const float* img, const float* gt, float w_l1, float w_ssim,
+                   float bias, void* workspace, float* out3, float* dL_dimg, void* stream);
+
 /* Upstream `markVisible` (never called by the reference; provided for API completeness).
  * present[i] = 1 iff view-space z > 0.2. */
 int d3g_mark_visible(int32_t N, const float* means3D, const float* viewmatrix, uint8_t* present,
