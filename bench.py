@@ -4,7 +4,7 @@
 One "step" = one (camera, timestamp) frame per GPU through the reference-facing API of this repo:
     d_xyz, d_rot, d_scale = DeformModelBaseline.step(xyz.detach(), fid.expand(N,1))   # fused tcgen05 MLP
     out = render(cam, gaussians, pipe, bg, d_xyz, d_rot, d_scale)                     # CUDA rasterizer
-    loss = l1(out["render"], gt); loss.backward()                                     # raster bwd + MLP bwd
+    loss = 0.8*l1(out["render"], gt) + 0.2*(1-ssim(out["render"], gt)); loss.backward()                                     # raster bwd + MLP bwd
 (scene/deform_model.py:323-324, gaussian_renderer/__init__.py:32-133, train_baseline.py:109-128).
 With N > 1 every rank renders its own frame of the camera/time batch and the Gaussian-parameter and MLP
 gradients are summed with one NCCL all-reduce over a flat buffer (weak scaling: one frame per GPU per step).
@@ -148,6 +148,7 @@ class Workload:
         self.model.deform.fused_grad_accumulation = True
         # sync-free frames: the binning workspace is sized from the largest pair count seen so far (+25 %) instead of
         # reading `num_rendered` back in the middle of every frame; overflow is checked where the host syncs anyway
+        self.training_loss = pkg("loss_utils").training_loss
         ras = pkg("rasterizer")
         self.capacity = ras.GrowingPairCapacity(1.25)
         ras.PAIR_CAPACITY_POLICY = self.capacity
@@ -181,7 +182,7 @@ class Workload:
         out = render(cam, g, self.pipe, self.bg, d_xyz, d_rot, d_scale, self.cfg["is_6dof"])
         if from_host:
             torch.cuda.current_stream().wait_event(self.gt_ready)
-        loss = (out["render"] - self.dev["gt"]).abs().mean()
+        loss = self.training_loss(out["render"], self.dev["gt"], 0.2)   # train_baseline.py:126-127, fused
         loss.backward()
         self.last = out
         if from_host:
@@ -408,7 +409,7 @@ def main():
             "data": "synthetic",
             "config": {"workload": "%s: %d Gaussians SH3 %dx%d deform MLP + rasterize fwd+bwd, 1 frame per GPU per step" %
                        (args.config, cfg["N"], cfg["W"], cfg["H"]), "is_6dof": cfg["is_6dof"],
-                       "net": "DeformNetworkBaseline(is_blender=True)", "loss": "L1 vs fixed random image",
+                       "net": "DeformNetworkBaseline(is_blender=True)", "loss": "0.8*L1 + 0.2*(1-SSIM) vs fixed random image (fused CUDA loss)",
                        "pair_capacity": "GrowingPairCapacity(1.25): no num_rendered read-back inside a frame",
                        "l2": "per-step working set (saved MLP activation tiles, ~1.7 GB at 100k points) exceeds the 126 MB L2",
                        "parallelism": "frame-parallel dp%d, one NCCL all-reduce of the flat gradient buffer" % world},

@@ -4,7 +4,7 @@
 // zero padding 5, one window per channel, C1 = 0.01^2, C2 = 0.03^2, mean over the map), and the
 // combination of train_baseline.py:126-127:  loss = (1 - lambda) * L1 + lambda * (1 - ssim).
 // The reference runs 5 grouped conv2d + ~15 elementwise launches forward and as many again in autograd; here
-//   ssim_fwd_kernel : one CTA per 16x16 pixel block of one channel stages a 26x26 halo of both images in shared
+//   ssim_fwd_kernel : one CTA per 32x16 pixel block of one channel stages a 42x26 halo of both images in shared
 //                     memory, runs the separable window (5 moments), evaluates the SSIM map, and stores the three
 //                     per-pixel partials dS/dmu1, dS/dE[x^2], dS/dE[xy] plus per-block partial sums of S and |x-y|;
 //   loss_reduce_kernel : deterministic tree sum of the partials -> {L1 mean, SSIM mean, combined loss};
@@ -16,9 +16,10 @@
 
 namespace d3g {
 
-constexpr int kLT = 16;            // pixel block edge
+constexpr int kTW = 32, kTH = 16;  // pixel block of one CTA (256 threads, two pixels each)
 constexpr int kHalo = 5;           // window 11
-constexpr int kLS = kLT + 2 * kHalo;  // 26
+constexpr int kSW = kTW + 2 * kHalo, kSH = kTH + 2 * kHalo;  // 42 x 26 staged halo
+constexpr int kLThreads = 256;
 
 __constant__ float c_win[11];
 static bool g_win_ready = false;
@@ -44,18 +45,17 @@ struct LossArgs {
   float* part;   // [blocks][2]: sum S, sum |x-y|
 };
 
-__global__ void __launch_bounds__(kLT * kLT)
+__global__ void __launch_bounds__(kLThreads)
 ssim_fwd_kernel(LossArgs a) {
-  __shared__ float s1[kLS][kLS + 1];
-  __shared__ float s2[kLS][kLS + 1];
-  __shared__ float h[5][kLS][kLT + 1];   // horizontally filtered moments
-  __shared__ float red[2][kLT * kLT / 32];
+  __shared__ float s1[kSH][kSW + 1];
+  __shared__ float s2[kSH][kSW + 1];
+  __shared__ float h[5][kSH][kTW + 1];   // horizontally filtered moments
+  __shared__ float red[2][kLThreads / 32];
   const int c = blockIdx.z;
-  const int x0 = blockIdx.x * kLT, y0 = blockIdx.y * kLT;
-  const int tx = threadIdx.x % kLT, ty = threadIdx.x / kLT;
+  const int x0 = blockIdx.x * kTW, y0 = blockIdx.y * kTH;
   const size_t plane = (size_t)c * a.H * a.W;
-  for (int i = threadIdx.x; i < kLS * kLS; i += kLT * kLT) {
-    const int ly = i / kLS, lx = i % kLS;
+  for (int i = threadIdx.x; i < kSH * kSW; i += kLThreads) {
+    const int ly = i / kSW, lx = i % kSW;
     const int gy = y0 + ly - kHalo, gx = x0 + lx - kHalo;
     float v1 = 0.f, v2 = 0.f;   // zero padding, as F.conv2d(padding=5)
     if (gy >= 0 && gy < a.H && gx >= 0 && gx < a.W) {
@@ -67,8 +67,8 @@ ssim_fwd_kernel(LossArgs a) {
   }
   __syncthreads();
   // horizontal pass: 26 rows x 16 columns, 5 moments each
-  for (int i = threadIdx.x; i < kLS * kLT; i += kLT * kLT) {
-    const int ly = i / kLT, lx = i % kLT;
+  for (int i = threadIdx.x; i < kSH * kTW; i += kLThreads) {
+    const int ly = i / kTW, lx = i % kTW;
     float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
 #pragma unroll
     for (int k = 0; k < 11; k++) {
@@ -78,29 +78,34 @@ ssim_fwd_kernel(LossArgs a) {
     h[0][ly][lx] = m1; h[1][ly][lx] = m2; h[2][ly][lx] = e11; h[3][ly][lx] = e22; h[4][ly][lx] = e12;
   }
   __syncthreads();
-  float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
-#pragma unroll
-  for (int k = 0; k < 11; k++) {
-    const float w = c_win[k];
-    mu1 += w * h[0][ty + k][tx]; mu2 += w * h[1][ty + k][tx];
-    e11 += w * h[2][ty + k][tx]; e22 += w * h[3][ty + k][tx]; e12 += w * h[4][ty + k][tx];
-  }
-  const int gx = x0 + tx, gy = y0 + ty;
-  const bool inside = gx < a.W && gy < a.H;
+  const int tx = threadIdx.x % kTW;
   float S = 0.f, l1 = 0.f;
-  if (inside) {
-    const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
-    const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
-    const float sig1 = e11 - mu1_sq, sig2 = e22 - mu2_sq, sig12 = e12 - mu12;
-    const float A1 = 2.f * mu12 + C1, A2 = 2.f * sig12 + C2, B1 = mu1_sq + mu2_sq + C1, B2 = sig1 + sig2 + C2;
-    const float inv = 1.0f / (B1 * B2);
-    S = A1 * A2 * inv;
-    const size_t o = plane + (size_t)gy * a.W + gx;
-    // partials of S w.r.t. the three moments that depend on img1 (sigma1^2 = E11 - mu1^2, sigma12 = E12 - mu1 mu2)
-    a.dmu[o] = 2.f * mu2 * (A2 - A1) * inv - S * 2.f * mu1 * (1.0f / B1 - 1.0f / B2);
-    a.d11[o] = -S / B2;
-    a.d12[o] = 2.f * A1 * inv;
-    l1 = fabsf(s1[ty + kHalo][tx + kHalo] - s2[ty + kHalo][tx + kHalo]);
+#pragma unroll
+  for (int r = 0; r < 2; r++) {
+    const int ty = threadIdx.x / kTW + r * (kLThreads / kTW);
+    float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+#pragma unroll
+    for (int k = 0; k < 11; k++) {
+      const float w = c_win[k];
+      mu1 += w * h[0][ty + k][tx]; mu2 += w * h[1][ty + k][tx];
+      e11 += w * h[2][ty + k][tx]; e22 += w * h[3][ty + k][tx]; e12 += w * h[4][ty + k][tx];
+    }
+    const int gx = x0 + tx, gy = y0 + ty;
+    if (gx < a.W && gy < a.H) {
+      const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
+      const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
+      const float sig1 = e11 - mu1_sq, sig2 = e22 - mu2_sq, sig12 = e12 - mu12;
+      const float A1 = 2.f * mu12 + C1, A2 = 2.f * sig12 + C2, B1 = mu1_sq + mu2_sq + C1, B2 = sig1 + sig2 + C2;
+      const float inv = 1.0f / (B1 * B2);
+      const float Sp = A1 * A2 * inv;
+      S += Sp;
+      const size_t o = plane + (size_t)gy * a.W + gx;
+      // partials of S w.r.t. the three moments that depend on img1 (sigma1^2 = E11 - mu1^2, sigma12 = E12 - mu1 mu2)
+      a.dmu[o] = 2.f * mu2 * (A2 - A1) * inv - Sp * 2.f * mu1 * (1.0f / B1 - 1.0f / B2);
+      a.d11[o] = -Sp / B2;
+      a.d12[o] = 2.f * A1 * inv;
+      l1 += fabsf(s1[ty + kHalo][tx + kHalo] - s2[ty + kHalo][tx + kHalo]);
+    }
   }
   // block partial sums (fixed order: deterministic)
 #pragma unroll
@@ -112,7 +117,7 @@ ssim_fwd_kernel(LossArgs a) {
   __syncthreads();
   if (threadIdx.x == 0) {
     float ts = 0.f, tl = 0.f;
-    for (int w = 0; w < kLT * kLT / 32; w++) { ts += red[0][w]; tl += red[1][w]; }
+    for (int w = 0; w < kLThreads / 32; w++) { ts += red[0][w]; tl += red[1][w]; }
     const size_t b = ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
     a.part[2 * b] = ts;
     a.part[2 * b + 1] = tl;
@@ -144,17 +149,16 @@ loss_reduce_kernel(const float* __restrict__ part, int blocks, float inv_n, floa
 }
 
 // dL/dimg = w_l1/n * sign(x - y) + w_ssim/n * [ win*dmu + 2 x (win*d11) + y (win*d12) ]
-__global__ void __launch_bounds__(kLT * kLT)
+__global__ void __launch_bounds__(kLThreads)
 ssim_bwd_kernel(LossArgs a, float w_l1_n, float w_ssim_n, float* __restrict__ dimg) {
-  __shared__ float s[3][kLS][kLS + 1];
-  __shared__ float h[3][kLS][kLT + 1];
+  __shared__ float s[3][kSH][kSW + 1];
+  __shared__ float h[3][kSH][kTW + 1];
   const int c = blockIdx.z;
-  const int x0 = blockIdx.x * kLT, y0 = blockIdx.y * kLT;
-  const int tx = threadIdx.x % kLT, ty = threadIdx.x / kLT;
+  const int x0 = blockIdx.x * kTW, y0 = blockIdx.y * kTH;
   const size_t plane = (size_t)c * a.H * a.W;
   if (w_ssim_n != 0.f) {
-    for (int i = threadIdx.x; i < kLS * kLS; i += kLT * kLT) {
-      const int ly = i / kLS, lx = i % kLS;
+    for (int i = threadIdx.x; i < kSH * kSW; i += kLThreads) {
+      const int ly = i / kSW, lx = i % kSW;
       const int gy = y0 + ly - kHalo, gx = x0 + lx - kHalo;
       float v0 = 0.f, v1 = 0.f, v2 = 0.f;
       if (gy >= 0 && gy < a.H && gx >= 0 && gx < a.W) {
@@ -164,8 +168,8 @@ ssim_bwd_kernel(LossArgs a, float w_l1_n, float w_ssim_n, float* __restrict__ di
       s[0][ly][lx] = v0; s[1][ly][lx] = v1; s[2][ly][lx] = v2;
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < kLS * kLT; i += kLT * kLT) {
-      const int ly = i / kLT, lx = i % kLT;
+    for (int i = threadIdx.x; i < kSH * kTW; i += kLThreads) {
+      const int ly = i / kTW, lx = i % kTW;
       float r0 = 0.f, r1 = 0.f, r2 = 0.f;
 #pragma unroll
       for (int k = 0; k < 11; k++) {
@@ -176,23 +180,28 @@ ssim_bwd_kernel(LossArgs a, float w_l1_n, float w_ssim_n, float* __restrict__ di
     }
     __syncthreads();
   }
-  const int gx = x0 + tx, gy = y0 + ty;
-  if (gx >= a.W || gy >= a.H) return;
-  const size_t o = plane + (size_t)gy * a.W + gx;
-  const float x = a.img[o], y = a.gt[o];
-  float g = 0.f;
-  if (w_ssim_n != 0.f) {
-    float r0 = 0.f, r1 = 0.f, r2 = 0.f;
+  const int tx = threadIdx.x % kTW;
 #pragma unroll
-    for (int k = 0; k < 11; k++) {
-      const float w = c_win[k];
-      r0 += w * h[0][ty + k][tx]; r1 += w * h[1][ty + k][tx]; r2 += w * h[2][ty + k][tx];
+  for (int r = 0; r < 2; r++) {
+    const int ty = threadIdx.x / kTW + r * (kLThreads / kTW);
+    const int gx = x0 + tx, gy = y0 + ty;
+    if (gx >= a.W || gy >= a.H) continue;
+    const size_t o = plane + (size_t)gy * a.W + gx;
+    const float x = a.img[o], y = a.gt[o];
+    float g = 0.f;
+    if (w_ssim_n != 0.f) {
+      float r0 = 0.f, r1 = 0.f, r2 = 0.f;
+#pragma unroll
+      for (int k = 0; k < 11; k++) {
+        const float w = c_win[k];
+        r0 += w * h[0][ty + k][tx]; r1 += w * h[1][ty + k][tx]; r2 += w * h[2][ty + k][tx];
+      }
+      g = w_ssim_n * (r0 + 2.f * x * r1 + y * r2);
     }
-    g = w_ssim_n * (r0 + 2.f * x * r1 + y * r2);
+    const float d = x - y;
+    g += w_l1_n * (d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f));   // torch.sign: 0 at 0
+    dimg[o] = g;
   }
-  const float d = x - y;
-  g += w_l1_n * (d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f));   // torch.sign: 0 at 0
-  dimg[o] = g;
 }
 
 }  // namespace d3g
@@ -203,7 +212,7 @@ extern "C" {
 
 int d3g_image_loss_workspace_bytes(int32_t C, int32_t H, int32_t W, size_t* bytes) {
   if (C < 1 || H < 1 || W < 1 || !bytes) return set_err(D3G_ERR_INVALID, "bad image_loss shape");
-  const size_t blocks = (size_t)C * ((H + kLT - 1) / kLT) * ((W + kLT - 1) / kLT);
+  const size_t blocks = (size_t)C * ((H + kTH - 1) / kTH) * ((W + kTW - 1) / kTW);
   *bytes = align_up(3 * (size_t)C * H * W * sizeof(float), 256) + align_up(2 * blocks * sizeof(float), 256);
   return 0;
 }
@@ -219,7 +228,7 @@ int d3g_image_loss(int32_t C, int32_t H, int32_t W, const float* img, const floa
     D3G_CUDA_TRY(cudaMemcpyToSymbol(c_win, w, sizeof(w)));
     g_win_ready = true;
   }
-  const dim3 grid((W + kLT - 1) / kLT, (H + kLT - 1) / kLT, C);
+  const dim3 grid((W + kTW - 1) / kTW, (H + kTH - 1) / kTH, C);
   const size_t blocks = (size_t)grid.x * grid.y * grid.z;
   if (blocks > 0x7fffffffull) return set_err(D3G_ERR_CAPACITY, "image too large");
   const size_t n = (size_t)C * H * W;
@@ -228,13 +237,13 @@ int d3g_image_loss(int32_t C, int32_t H, int32_t W, const float* img, const floa
   a.dmu = (float*)workspace; a.d11 = a.dmu + n; a.d12 = a.d11 + n;
   a.part = (float*)((uint8_t*)workspace + align_up(3 * n * sizeof(float), 256));
   { ProfScope _p(PROF_LOSS_FWD, stream);
-    ssim_fwd_kernel<<<grid, kLT * kLT, 0, stream>>>(a);
+    ssim_fwd_kernel<<<grid, kLThreads, 0, stream>>>(a);
     D3G_LAUNCH_CHECK(0, stream);
     loss_reduce_kernel<<<1, 1024, 0, stream>>>(a.part, (int)blocks, (float)(1.0 / (double)n), w_l1, w_ssim, bias, out3);
     D3G_LAUNCH_CHECK(0, stream); }
   if (dL_dimg) {
     ProfScope _p(PROF_LOSS_BWD, stream);
-    ssim_bwd_kernel<<<grid, kLT * kLT, 0, stream>>>(a, (float)(w_l1 / (double)n), (float)(w_ssim / (double)n), dL_dimg);
+    ssim_bwd_kernel<<<grid, kLThreads, 0, stream>>>(a, (float)(w_l1 / (double)n), (float)(w_ssim / (double)n), dL_dimg);
     D3G_LAUNCH_CHECK(0, stream);
   }
   return 0;
