@@ -290,7 +290,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
           tmem_wait_ld();
           const uint32_t bits = mbits[i];
 #pragma unroll
-          for (int k = 0; k < 32; k++) v[k] = ((bits >> k) & 1u) ? to_tf32(__uint_as_float(v[k])) : 0u;
+          for (int k = 0; k < 32; k++) v[k] = ((bits >> k) & 1u) ? tf32_rna_bits(v[k]) : 0u;
           if (j < 7) {
             tmem_st32(lane_addr + half + c * 32, v);
             tmem_wait_st();

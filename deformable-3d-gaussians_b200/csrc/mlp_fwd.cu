@@ -281,12 +281,16 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
             const float4 b4 = ((const float4*)(bl + c * 32))[j];
             bv[4 * j] = b4.x; bv[4 * j + 1] = b4.y; bv[4 * j + 2] = b4.z; bv[4 * j + 3] = b4.w;
           }
+          // bias + ReLU + tf32 rounding + activity bit in five instructions per element (1 FADD, 1 integer add,
+          // 3 logic/shift): x is rounded on its bit pattern, `neg` is its sign smeared over the word, the
+          // activation is r & ~neg and the mask bit ~neg & (1 << j).  (x == +0 counts as active with value 0.)
 #pragma unroll
           for (int j = 0; j < 32; j++) {
-            float h = __uint_as_float(v[j]) + bv[j];
-            h = fmaxf(h, 0.f);
-            bits |= (h > 0.f ? 1u : 0u) << j;
-            v[j] = to_tf32(h);
+            const uint32_t r = __float_as_uint(__uint_as_float(v[j]) + bv[j]) + 0x1000u;
+            uint32_t neg;
+            asm("shr.s32 %0, %1, 31;" : "=r"(neg) : "r"(r));
+            asm("lop3.b32 %0, %1, %2, %3, 0x20;" : "=r"(v[j]) : "r"(r), "r"(neg), "r"(0xFFFFE000u));   // r & ~neg & C
+            asm("lop3.b32 %0, %0, %1, %2, 0xF2;" : "+r"(bits) : "r"(neg), "r"(1u << j));               // bits | (~neg & bit)
           }
           tmem_st32(lane_addr + half + c * 32, v);
           // hand the chunk to the MMA warp first, then save it for backward

@@ -207,4 +207,9 @@ __device__ __forceinline__ uint32_t to_tf32(float x) {
   return r;
 }
 
+// Same rounding on the bit pattern, for finite inputs: add half an ulp of the 10-bit mantissa, drop the low 13 bits
+// (magnitude rounding, ties away from zero = cvt.rna).  One integer add + one logic op instead of the guarded
+// sequence the compiler emits for cvt.rna.tf32 — the epilogues are ALU-pipe bound.  Inf/NaN stay non-finite.
+__device__ __forceinline__ uint32_t tf32_rna_bits(uint32_t bits) { return (bits + 0x1000u) & 0xFFFFE000u; }
+
 }  // namespace d3g
