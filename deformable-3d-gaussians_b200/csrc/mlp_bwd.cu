@@ -304,14 +304,18 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
           if (lane == 0) bulk_wait_read<0>();
           __syncwarp();
           const bool swap = (lane >> 2) & 1;
-          uint8_t* line = stg + lane * 128 + (swap ? 16 : 0);
+          const uint32_t line = smem_u32(stg) + lane * 128 + (swap ? 16 : 0);
 #pragma unroll
           for (int j8 = 0; j8 < 4; j8++) {
-            uint8_t* d = line + ((j8 ^ (lane & 3)) << 5);
-            const uint4 lo = make_uint4(v[8 * j8], v[8 * j8 + 1], v[8 * j8 + 2], v[8 * j8 + 3]);
-            const uint4 hi = make_uint4(v[8 * j8 + 4], v[8 * j8 + 5], v[8 * j8 + 6], v[8 * j8 + 7]);
-            *(uint4*)d = swap ? hi : lo;
-            *(uint4*)((uintptr_t)d ^ 16) = swap ? lo : hi;
+            const uint32_t d = line + ((j8 ^ (lane & 3)) << 5);
+            // two straight-line variants (the lane quads diverge once) instead of 32 value selects
+            if (swap) {
+              sts128(d, v[8 * j8 + 4], v[8 * j8 + 5], v[8 * j8 + 6], v[8 * j8 + 7]);
+              sts128(d ^ 16u, v[8 * j8], v[8 * j8 + 1], v[8 * j8 + 2], v[8 * j8 + 3]);
+            } else {
+              sts128(d, v[8 * j8], v[8 * j8 + 1], v[8 * j8 + 2], v[8 * j8 + 3]);
+              sts128(d ^ 16u, v[8 * j8 + 4], v[8 * j8 + 5], v[8 * j8 + 6], v[8 * j8 + 7]);
+            }
           }
           fence_proxy_async();
           __syncwarp();

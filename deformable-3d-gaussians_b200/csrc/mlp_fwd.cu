@@ -276,9 +276,10 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
           tmem_wait_ld();
           uint32_t bits = 0;
           float bv[32];
+          const uint32_t bl_s = smem_u32(bl + c * 32);
 #pragma unroll
           for (int j = 0; j < 8; j++) {
-            const float4 b4 = ((const float4*)(bl + c * 32))[j];
+            const float4 b4 = lds128f(bl_s + 16 * j);
             bv[4 * j] = b4.x; bv[4 * j + 1] = b4.y; bv[4 * j + 2] = b4.z; bv[4 * j + 3] = b4.w;
           }
           // bias + ReLU + tf32 rounding + activity bit in five instructions per element (1 FADD, 1 integer add,
@@ -306,14 +307,18 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
             if (lane == 0) bulk_wait_read<0>();   // previous block has left the staging buffer
             __syncwarp();
             const bool swap = (lane >> 2) & 1;    // odd lane quads write the two 16 B halves in the other order
-            uint8_t* line = stg + lane * 128 + (swap ? 16 : 0);
+            const uint32_t line = smem_u32(stg) + lane * 128 + (swap ? 16 : 0);
 #pragma unroll
             for (int j8 = 0; j8 < 4; j8++) {
-              uint8_t* d = line + ((j8 ^ (lane & 3)) << 5);
-              const uint4 lo = make_uint4(v[8 * j8], v[8 * j8 + 1], v[8 * j8 + 2], v[8 * j8 + 3]);
-              const uint4 hi = make_uint4(v[8 * j8 + 4], v[8 * j8 + 5], v[8 * j8 + 6], v[8 * j8 + 7]);
-              *(uint4*)d = swap ? hi : lo;
-              *(uint4*)((uintptr_t)d ^ 16) = swap ? lo : hi;
+              const uint32_t d = line + ((j8 ^ (lane & 3)) << 5);
+              // two straight-line variants (the lane quads diverge once) instead of 32 value selects
+              if (swap) {
+                sts128(d, v[8 * j8 + 4], v[8 * j8 + 5], v[8 * j8 + 6], v[8 * j8 + 7]);
+                sts128(d ^ 16u, v[8 * j8], v[8 * j8 + 1], v[8 * j8 + 2], v[8 * j8 + 3]);
+              } else {
+                sts128(d, v[8 * j8], v[8 * j8 + 1], v[8 * j8 + 2], v[8 * j8 + 3]);
+                sts128(d ^ 16u, v[8 * j8 + 4], v[8 * j8 + 5], v[8 * j8 + 6], v[8 * j8 + 7]);
+              }
             }
             fence_proxy_async();
             __syncwarp();

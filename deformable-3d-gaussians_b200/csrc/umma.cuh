@@ -207,6 +207,17 @@ __device__ __forceinline__ uint32_t to_tf32(float x) {
   return r;
 }
 
+// explicit shared-window accesses: the dynamic-smem pointers reach the epilogues as generic pointers, and the
+// generic LD/ST forms cost an extra R2UR pair each
+__device__ __forceinline__ void sts128(uint32_t saddr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ float4 lds128f(uint32_t saddr) {
+  float4 r;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(saddr));
+  return r;
+}
+
 // Same rounding on the bit pattern, for finite inputs: add half an ulp of the 10-bit mantissa, drop the low 13 bits
 // (magnitude rounding, ties away from zero = cvt.rna).  One integer add + one logic op instead of the guarded
 // sequence the compiler emits for cvt.rna.tf32 — the epilogues are ALU-pipe bound.  Inf/NaN stay non-finite.
