@@ -150,12 +150,17 @@ loss_reduce_kernel(const float* __restrict__ part, int blocks, float inv_n, floa
 
 // dL/dimg = w_l1/n * sign(x - y) + w_ssim/n * [ win*dmu + 2 x (win*d11) + y (win*d12) ]
 __global__ void __launch_bounds__(kLThreads)
-ssim_bwd_kernel(LossArgs a, float w_l1_n, float w_ssim_n, float* __restrict__ dimg) {
+ssim_bwd_kernel(LossArgs a, float w_l1_n, float w_ssim_n, const float* __restrict__ upstream, float* __restrict__ dimg) {
   __shared__ float s[3][kSH][kSW + 1];
   __shared__ float h[3][kSH][kTW + 1];
   const int c = blockIdx.z;
   const int x0 = blockIdx.x * kTW, y0 = blockIdx.y * kTH;
   const size_t plane = (size_t)c * a.H * a.W;
+  if (upstream) {   // cotangent of the scalar loss (device scalar), folded in here instead of a separate pass
+    const float u = __ldg(upstream);
+    w_l1_n *= u;
+    w_ssim_n *= u;
+  }
   if (w_ssim_n != 0.f) {
     for (int i = threadIdx.x; i < kSH * kSW; i += kLThreads) {
       const int ly = i / kSW, lx = i % kSW;
@@ -241,11 +246,26 @@ int d3g_image_loss(int32_t C, int32_t H, int32_t W, const float* img, const floa
     D3G_LAUNCH_CHECK(0, stream);
     loss_reduce_kernel<<<1, 1024, 0, stream>>>(a.part, (int)blocks, (float)(1.0 / (double)n), w_l1, w_ssim, bias, out3);
     D3G_LAUNCH_CHECK(0, stream); }
-  if (dL_dimg) {
-    ProfScope _p(PROF_LOSS_BWD, stream);
-    ssim_bwd_kernel<<<grid, kLThreads, 0, stream>>>(a, (float)(w_l1 / (double)n), (float)(w_ssim / (double)n), dL_dimg);
-    D3G_LAUNCH_CHECK(0, stream);
-  }
+  if (dL_dimg) return d3g_image_loss_backward(C, H, W, img, gt, w_l1, w_ssim, workspace, nullptr, dL_dimg, stream_);
+  return 0;
+}
+
+int d3g_image_loss_backward(int32_t C, int32_t H, int32_t W, const float* img, const float* gt, float w_l1,
+                            float w_ssim, const void* workspace, const float* upstream, float* dL_dimg,
+                            void* stream_) {
+  if (C < 1 || H < 1 || W < 1) return set_err(D3G_ERR_INVALID, "bad image_loss shape");
+  if (!img || !gt || !workspace || !dL_dimg) return set_err(D3G_ERR_INVALID, "NULL argument");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  const dim3 grid((W + kTW - 1) / kTW, (H + kTH - 1) / kTH, C);
+  const size_t n = (size_t)C * H * W;
+  LossArgs a;
+  a.C = C; a.H = H; a.W = W; a.img = img; a.gt = gt;
+  a.dmu = (float*)workspace; a.d11 = a.dmu + n; a.d12 = a.d11 + n;
+  a.part = nullptr;
+  { ProfScope _p(PROF_LOSS_BWD, stream);
+    ssim_bwd_kernel<<<grid, kLThreads, 0, stream>>>(a, (float)(w_l1 / (double)n), (float)(w_ssim / (double)n), upstream,
+                                                    dL_dimg);
+    D3G_LAUNCH_CHECK(0, stream); }
   return 0;
 }
 

@@ -11,7 +11,8 @@ from . import _lib
 
 class _ImageLoss(torch.autograd.Function):
     """value = w_l1 * mean|img - gt| + w_ssim * mean SSIM(img, gt) + bias; gradient w.r.t. img only (the reference
-    never differentiates the ground truth).  The gradient is produced in the forward pass; backward scales it."""
+    never differentiates the ground truth).  Forward leaves three per-pixel partial maps in a workspace; backward turns them into the gradient, scaled by the
+    upstream cotangent inside the same kernel."""
 
     @staticmethod
     def forward(ctx, img, gt, w_l1, w_ssim, bias):
@@ -28,19 +29,25 @@ class _ImageLoss(torch.autograd.Function):
         _lib.check(lib.d3g_image_loss_workspace_bytes(Cn, H, W, C.byref(nb)))
         ws = torch.empty(nb.value, dtype=torch.uint8, device=x.device)
         out = torch.empty(3, dtype=torch.float32, device=x.device)
-        need_grad = ctx.needs_input_grad[0]
-        grad = torch.empty_like(x) if need_grad else None
         _lib.check(lib.d3g_image_loss(Cn, H, W, _lib.ptr(x), _lib.ptr(y), C.c_float(w_l1), C.c_float(w_ssim),
-                                      C.c_float(bias), _lib.ptr(ws), _lib.ptr(out), _lib.ptr(grad),
+                                      C.c_float(bias), _lib.ptr(ws), _lib.ptr(out), None,
                                       C.c_void_p(torch.cuda.current_stream().cuda_stream)))
-        ctx.grad = grad
+        ctx.saved = (x, y, ws, Cn, H, W, w_l1, w_ssim, img.shape)
         ctx.terms = out
         return out[2]
 
     @staticmethod
     def backward(ctx, g):
-        grad = ctx.grad
-        return (None if grad is None else grad * g), None, None, None, None
+        if not ctx.needs_input_grad[0]:
+            return None, None, None, None, None
+        lib = _lib.load()
+        x, y, ws, Cn, H, W, w_l1, w_ssim, shape = ctx.saved
+        g = g.detach().reshape(1).float().contiguous()
+        grad = torch.empty_like(x)
+        _lib.check(lib.d3g_image_loss_backward(Cn, H, W, _lib.ptr(x), _lib.ptr(y), C.c_float(w_l1), C.c_float(w_ssim),
+                                               _lib.ptr(ws), _lib.ptr(g), _lib.ptr(grad),
+                                               C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        return grad.view(shape), None, None, None, None
 
 
 def l1_loss(network_output, gt):

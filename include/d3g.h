@@ -141,6 +141,11 @@ int d3g_gaussians_prepare_backward(int32_t N, int32_t is_6dof, const float* xyz,
 int d3g_image_loss_workspace_bytes(int32_t C, int32_t H, int32_t W, size_t* bytes);
 int d3g_image_loss(int32_t C, int32_t H, int32_t W, const float* img, const float* gt, float w_l1, float w_ssim,
                    float bias, void* workspace, float* out3, float* dL_dimg, void* stream);
+/* The gradient alone, from the workspace a d3g_image_loss call on the same img/gt left behind: dL_dimg =
+ * upstream * d(out3[2])/d(img); upstream is a device scalar (the cotangent autograd hands to backward) or NULL = 1. */
+int d3g_image_loss_backward(int32_t C, int32_t H, int32_t W, const float* img, const float* gt, float w_l1,
+                            float w_ssim, const void* workspace, const float* upstream, float* dL_dimg,
+                            void* stream);
 
 /* Upstream `markVisible` (never called by the reference; provided for API completeness).
  * present[i] = 1 iff view-space z > 0.2. */

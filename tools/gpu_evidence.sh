@@ -10,7 +10,7 @@ timeout 300 python bench.py --impl reference --steps 2 --warmup 1 > $O/${T}_ref.
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file $O/${T}_launches.csv \
   python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-roofline > $O/${T}_ncu_launch.log 2>&1; echo "launchlist rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on \
-  -k regex:"mlp_fwd_kernel|mlp_dgrad_kernel|mlp_wgrad_kernel|render_fwd_kernel|render_bwd_kernel|preprocess_fwd_kernel|preprocess_bwd_kernel|duplicate_with_keys_kernel|DeviceRadixSortOnesweep|gaussians_prepare" \
+  -k regex:"ssim_fwd_kernel|ssim_bwd_kernel|mlp_fwd_kernel|mlp_dgrad_kernel|mlp_wgrad_kernel|render_fwd_kernel|render_bwd_kernel|preprocess_fwd_kernel|preprocess_bwd_kernel|duplicate_with_keys_kernel|DeviceRadixSortOnesweep|gaussians_prepare" \
   --launch-skip 60 --launch-count 20 -o $O/${T}_top -f python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-roofline > $O/${T}_ncu_full.log 2>&1; echo "full rc=$?"
 ncu -i $O/${T}_top.ncu-rep --page raw --csv > $O/${T}_raw.csv 2>/dev/null
 head -c 1200 $O/${T}_bench.json
