@@ -140,9 +140,11 @@ class Workload:
         self.pipe = type("Pipe", (), dict(convert_SHs_python=False, compute_cov3D_python=False, debug=False))()
         # flat gradient buffer: parameter .grad tensors are views into it, so the multi-GPU exchange is
         # one all-reduce with no packing kernel
-        # with several ranks the Gaussian slice is all-reduced while the MLP backward still runs
+        # D3G_BENCH_EARLY=1: all-reduce the Gaussian slice from inside backward, overlapping the MLP backward.  Measured
+        # at 4 GPUs it does not pay (the persistent MLP kernels own every SM, the NCCL CTAs only delay them): 1.62k vs
+        # 1.70k frames/s end to end, so the default is one all-reduce after backward
         self.grads = pkg("frames").FlatGrads(g.parameters() + list(self.model.deform.parameters()),
-                                             early=len(g.parameters()) if world > 1 else 0)
+                                             early=len(g.parameters()) if (world > 1 and os.environ.get("D3G_BENCH_EARLY", "0") == "1") else 0)
         self.flat = self.grads.flat
         # MLP backward adds straight into those .grad views (no per-parameter zero-fill + AccumulateGrad add)
         self.model.deform.fused_grad_accumulation = True
@@ -201,10 +203,20 @@ def timed_region(work, steps, from_host, world, dist):
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
+    # the host may run at most `depth` frames ahead of the device (launch latency stays hidden, the queues of
+    # several ranks cannot drift arbitrarily far apart); 0 = unbounded
+    depth = int(os.environ.get("D3G_BENCH_INFLIGHT", "2"))
+    marks = []
     for _ in range(steps):
+        if depth and len(marks) >= depth:
+            marks.pop(0).synchronize()
         work.frame(from_host)
         if world > 1:
             work.grads.all_reduce()
+        if depth:
+            ev = torch.cuda.Event()
+            ev.record()
+            marks.append(ev)
     e1.record()
     torch.cuda.synchronize()
     work.capacity.check()
@@ -412,7 +424,7 @@ def main():
                        "net": "DeformNetworkBaseline(is_blender=True)", "loss": "0.8*L1 + 0.2*(1-SSIM) vs fixed random image (fused CUDA loss)",
                        "pair_capacity": "GrowingPairCapacity(1.25): no num_rendered read-back inside a frame",
                        "l2": "per-step working set (saved MLP activation tiles, ~1.7 GB at 100k points) exceeds the 126 MB L2",
-                       "parallelism": "frame-parallel dp%d, one NCCL all-reduce of the flat gradient buffer" % world},
+                       "parallelism": "frame-parallel dp%d, one NCCL all-reduce of the flat gradient buffer, <= 2 frames in flight" % world},
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": work.h2d_bytes, "d2h_bytes_per_step": 4,
                     "ms_per_step": sec_e2e / args.steps * 1e3},
             "clocks": sampler.summary()}
