@@ -75,6 +75,11 @@ class RasterSettings(C.Structure):
                 ("densify_mode", C.c_int32)]
 
 
+class AdamTensor(C.Structure):
+    _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+                ("numel", C.c_int64), ("lr", C.c_float), ("weight_decay", C.c_float), ("step", C.c_int64)]
+
+
 class MlpConfig(C.Structure):
     _fields_ = [("is_blender", C.c_int32), ("is_6dof", C.c_int32), ("heads", C.c_int32),
                 ("D", C.c_int32), ("W", C.c_int32), ("multires", C.c_int32)]
@@ -105,7 +110,7 @@ EXPORTS = ["d3g_last_error", "d3g_version", "d3g_prof_enable", "d3g_prof_count",
            "d3g_mark_visible", "d3g_gaussians_prepare", "d3g_gaussians_prepare_backward", "d3g_raster_read_header", "d3g_raster_header_async", "d3g_raster_read_state", "d3g_mlp_packed_bytes",
            "d3g_mlp_workspace_bytes", "d3g_mlp_pack_weights", "d3g_mlp_forward", "d3g_mlp_backward", "d3g_mlp_read_status", "d3g_mlp_read_masks",
            "d3g_selftest_umma", "d3g_selftest_umma_raw", "d3g_selftest_umma_clk", "d3g_image_loss_workspace_bytes",
-           "d3g_image_loss", "d3g_image_loss_backward"]
+           "d3g_image_loss", "d3g_image_loss_backward", "d3g_adam_step"]
 
 _lib = None
 

@@ -17,6 +17,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib
+from .optim import Adam as _FusedAdam  # torch.optim.Adam subclass: same state/param_groups, one fused step kernel
 
 HEAD_WARP, HEAD_ROT, HEAD_SCALE = 1, 2, 4
 
@@ -338,7 +339,7 @@ class DeformModel(_DeformModelBase):
     def train_setting(self, training_args):
         l = [{"params": list(self.deform.parameters()),
               "lr": training_args.position_lr_init * self.spatial_lr_scale, "name": "deform"}]
-        self.optimizer = torch.optim.Adam(l, lr=0.0, eps=1e-15, weight_decay=training_args.weight_decay)
+        self.optimizer = _FusedAdam(l, lr=0.0, eps=1e-15, weight_decay=training_args.weight_decay)
         if self.scale_lr:
             lr_init = training_args.position_lr_init * self.spatial_lr_scale * training_args.num_cams_per_iter
             lr_final = training_args.position_lr_final * training_args.num_cams_per_iter
@@ -365,7 +366,7 @@ class DeformModelBaseline(_DeformModelBase):
     def train_setting(self, training_args):
         l = [{"params": list(self.deform.parameters()),
               "lr": training_args.position_lr_init * self.spatial_lr_scale, "name": "deform"}]
-        self.optimizer = torch.optim.Adam(l, lr=0.0, eps=1e-15)
+        self.optimizer = _FusedAdam(l, lr=0.0, eps=1e-15)
         self.deform_scheduler_args = get_expon_lr_func(
             lr_init=training_args.position_lr_init * self.spatial_lr_scale,
             lr_final=training_args.position_lr_final, lr_delay_mult=training_args.position_lr_delay_mult,

@@ -147,6 +147,23 @@ int d3g_image_loss_backward(int32_t C, int32_t H, int32_t W, const float* img, c
                             float w_ssim, const void* workspace, const float* upstream, float* dL_dimg,
                             void* stream);
 
+/* Fused multi-tensor Adam step: what `optimizer.step()` of scene/gaussian_model.py:136 and
+ * scene/deform_model.py:295,337 (torch.optim.Adam, betas (0.9, 0.999), eps 1e-15, optional weight_decay, no amsgrad)
+ * does for every parameter, in one launch.  `step` is the 1-based step count AFTER this update (torch increments
+ * before use); all pointers are fp32 device arrays of `numel` elements, updated in place. */
+typedef struct d3g_adam_tensor {
+  float* param;
+  const float* grad;
+  float* exp_avg;
+  float* exp_avg_sq;
+  int64_t numel;
+  float lr;
+  float weight_decay;
+  int64_t step;
+} d3g_adam_tensor;
+int d3g_adam_step(int32_t n_tensors, const d3g_adam_tensor* tensors, float beta1, float beta2, float eps,
+                  void* stream);
+
 /* Upstream `markVisible` (never called by the reference; provided for API completeness).
  * present[i] = 1 iff view-space z > 0.2. */
 int d3g_mark_visible(int32_t N, const float* means3D, const float* viewmatrix, uint8_t* present,
