@@ -794,8 +794,13 @@ preprocess_bwd_kernel(RasterArgs a, const float* __restrict__ means3D, const flo
   float dsc[3] = {0.f, 0.f, 0.f};
   float dq[4] = {0.f, 0.f, 0.f, 0.f};
   int nb = (a.sh_degree + 1) * (a.sh_degree + 1);
+  // dL/dSH of a Gaussian is basis[k] * dRGB[c]: kept in registers and written after the branch by the whole warp
+  // (invisible Gaussians write zeros), through shared memory so that the stores are contiguous runs instead of
+  // 48 scalar stores at a 192-byte lane stride
+  float shb[16], shg[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+  for (int k = 0; k < 16; k++) shb[k] = 0.f;
   if (!vis) {
-    if (dL_dsh) for (int k = 0; k < a.M * 3; k++) dL_dsh[si * a.M * 3 + k] = 0.f;
     if (dL_dcolors_precomp) for (int k = 0; k < 3; k++) dL_dcolors_precomp[3 * si + k] = 0.f;
   } else {
     float p[3] = {means3D[3 * si], means3D[3 * si + 1], means3D[3 * si + 2]};
@@ -879,13 +884,16 @@ preprocess_bwd_kernel(RasterArgs a, const float* __restrict__ means3D, const flo
       uint8_t cb = clamped[i];
       float dRGB[3] = {(cb & 1) ? 0.f : gcol.x, (cb & 2) ? 0.f : gcol.y, (cb & 4) ? 0.f : gcol.z};
       const float* sh = shs + si * a.M * 3;
-      float* dsh = dL_dsh + si * a.M * 3;
       float sdot[16];
-      for (int k = 0; k < a.M; k++) {
-        float bk = k < nb ? b[k] : 0.f;
-        if (k < nb && k < 16) sdot[k] = sh[3 * k] * dRGB[0] + sh[3 * k + 1] * dRGB[1] + sh[3 * k + 2] * dRGB[2];
-        dsh[3 * k] = bk * dRGB[0]; dsh[3 * k + 1] = bk * dRGB[1]; dsh[3 * k + 2] = bk * dRGB[2];
+#pragma unroll
+      for (int k = 0; k < 16; k++) {
+        sdot[k] = 0.f;
+        if (k < nb && k < a.M) {
+          sdot[k] = sh[3 * k] * dRGB[0] + sh[3 * k + 1] * dRGB[1] + sh[3 * k + 2] * dRGB[2];
+          shb[k] = b[k];
+        }
       }
+      shg[0] = dRGB[0]; shg[1] = dRGB[1]; shg[2] = dRGB[2];
       float x = d[0], y = d[1], z = d[2];
       float ddx = 0.f, ddy = 0.f, ddz = 0.f;
       if (a.sh_degree > 0) {
@@ -957,6 +965,31 @@ preprocess_bwd_kernel(RasterArgs a, const float* __restrict__ means3D, const flo
   if (dL_dcov3D) {
 #pragma unroll
     for (int k = 0; k < 6; k++) dL_dcov3D[6 * si + k] = dcov[k];
+  }
+  if (dL_dsh) {
+    __shared__ float s_sh[256 / 32][32][25];   // one 24-float slice of 32 Gaussians per warp (+1 pad: no bank conflicts)
+    // the lanes of this warp that hold a Gaussian (the last warp of the grid may be partial); named explicitly —
+    // __activemask() would only report the lanes that happen to have reconverged after the branches above
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int cnt = min(32, a.N - (i - lane));
+    const unsigned mask = cnt >= 32 ? 0xffffffffu : ((1u << cnt) - 1u);
+    const int row = 3 * a.M;                   // floats per Gaussian
+    float* out = dL_dsh + (si - lane) * row;   // first Gaussian of this warp
+#pragma unroll
+    for (int h = 0; h < 2; h++) {              // coefficients 0..7 and 8..15 (register indices stay compile-time)
+      const int base = 24 * h;
+      if (base >= row) break;
+      const int len = min(24, row - base);
+#pragma unroll
+      for (int j = 0; j < 24; j++) s_sh[warp][lane][j] = shb[(base + j) / 3] * shg[(base + j) % 3];
+      __syncwarp(mask);
+      for (int idx = lane; idx < cnt * len; idx += cnt) {   // only lanes 0..cnt-1 exist in a partial warp
+        const int g = idx / len, j = idx - g * len;
+        out[(size_t)g * row + base + j] = s_sh[warp][g][j];
+      }
+      __syncwarp(mask);
+    }
+    for (int e = 48; e < row; e++) dL_dsh[si * row + e] = 0.f;   // coefficients past degree 3 (M > 16) get no gradient
   }
 }
 
