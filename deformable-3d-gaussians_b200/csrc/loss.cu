@@ -80,16 +80,26 @@ ssim_fwd_kernel(LossArgs a) {
   __syncthreads();
   const int tx = threadIdx.x % kTW;
   float S = 0.f, l1 = 0.f;
+  // a thread owns two vertically adjacent pixels: their windows share 10 of 11 rows, so the column is read once
+  const int ty0 = (threadIdx.x / kTW) * 2;
+  float vm[2][5];
+#pragma unroll
+  for (int r = 0; r < 2; r++)
+#pragma unroll
+    for (int m = 0; m < 5; m++) vm[r][m] = 0.f;
+#pragma unroll
+  for (int k = 0; k < 12; k++) {
+#pragma unroll
+    for (int m = 0; m < 5; m++) {
+      const float v = h[m][ty0 + k][tx];
+      if (k < 11) vm[0][m] += c_win[k] * v;
+      if (k >= 1) vm[1][m] += c_win[k - 1] * v;
+    }
+  }
 #pragma unroll
   for (int r = 0; r < 2; r++) {
-    const int ty = threadIdx.x / kTW + r * (kLThreads / kTW);
-    float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
-#pragma unroll
-    for (int k = 0; k < 11; k++) {
-      const float w = c_win[k];
-      mu1 += w * h[0][ty + k][tx]; mu2 += w * h[1][ty + k][tx];
-      e11 += w * h[2][ty + k][tx]; e22 += w * h[3][ty + k][tx]; e12 += w * h[4][ty + k][tx];
-    }
+    const int ty = ty0 + r;
+    const float mu1 = vm[r][0], mu2 = vm[r][1], e11 = vm[r][2], e22 = vm[r][3], e12 = vm[r][4];
     const int gx = x0 + tx, gy = y0 + ty;
     if (gx < a.W && gy < a.H) {
       const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
@@ -186,23 +196,28 @@ ssim_bwd_kernel(LossArgs a, float w_l1_n, float w_ssim_n, const float* __restric
     __syncthreads();
   }
   const int tx = threadIdx.x % kTW;
+  const int ty0 = (threadIdx.x / kTW) * 2;
+  float vr[2][3] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}};
+  if (w_ssim_n != 0.f) {
+#pragma unroll
+    for (int k = 0; k < 12; k++) {
+#pragma unroll
+      for (int m = 0; m < 3; m++) {
+        const float v = h[m][ty0 + k][tx];
+        if (k < 11) vr[0][m] += c_win[k] * v;
+        if (k >= 1) vr[1][m] += c_win[k - 1] * v;
+      }
+    }
+  }
 #pragma unroll
   for (int r = 0; r < 2; r++) {
-    const int ty = threadIdx.x / kTW + r * (kLThreads / kTW);
+    const int ty = ty0 + r;
     const int gx = x0 + tx, gy = y0 + ty;
     if (gx >= a.W || gy >= a.H) continue;
     const size_t o = plane + (size_t)gy * a.W + gx;
     const float x = a.img[o], y = a.gt[o];
     float g = 0.f;
-    if (w_ssim_n != 0.f) {
-      float r0 = 0.f, r1 = 0.f, r2 = 0.f;
-#pragma unroll
-      for (int k = 0; k < 11; k++) {
-        const float w = c_win[k];
-        r0 += w * h[0][ty + k][tx]; r1 += w * h[1][ty + k][tx]; r2 += w * h[2][ty + k][tx];
-      }
-      g = w_ssim_n * (r0 + 2.f * x * r1 + y * r2);
-    }
+    if (w_ssim_n != 0.f) g = w_ssim_n * (vr[r][0] + 2.f * x * vr[r][1] + y * vr[r][2]);
     const float d = x - y;
     g += w_l1_n * (d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f));   // torch.sign: 0 at 0
     dimg[o] = g;

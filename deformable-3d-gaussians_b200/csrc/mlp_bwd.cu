@@ -604,8 +604,11 @@ __global__ void __launch_bounds__(256) mlp_finish_kernel(MlpFinishArgs a) {
   }
   {
     const int warp = tid >> 5, lane = tid & 31;
+    // (independent loads issued together: this single-CTA kernel is pure latency)
+#pragma unroll
     for (int j = warp; j < 30; j += 8) {
       float acc = 0.f;
+#pragma unroll
       for (int o = lane; o < 256; o += 32)
         acc += a.db_fresh[o] * a.w0[(size_t)o * a.pe_dim + 63 + j] +
                a.db_fresh[256 + o] * a.w5[(size_t)o * (a.pe_dim + 256) + 63 + j];
@@ -619,14 +622,22 @@ __global__ void __launch_bounds__(256) mlp_finish_kernel(MlpFinishArgs a) {
   const int k = tid;
   const float hk = a.thidden[k];
   float dh = 0.f;
+  float gw[30], tw[30];
+#pragma unroll
+  for (int i = 0; i < 30; i++) { gw[i] = a.g_tn2_w[i * 256 + k]; tw[i] = a.tn2_w[i * 256 + k]; }
+#pragma unroll
   for (int i = 0; i < 30; i++) {
-    a.g_tn2_w[i * 256 + k] += dtf[i] * hk;
-    dh += a.tn2_w[i * 256 + k] * dtf[i];
+    a.g_tn2_w[i * 256 + k] = gw[i] + dtf[i] * hk;
+    dh += tw[i] * dtf[i];
   }
   if (k < 30) a.g_tn2_b[k] += dtf[k];
   if (!(hk > 0.f)) dh = 0.f;
   a.g_tn0_b[k] += dh;
-  for (int c = 0; c < 13; c++) a.g_tn0_w[k * 13 + c] += dh * e[c];
+  float g0[13];
+#pragma unroll
+  for (int c = 0; c < 13; c++) g0[c] = a.g_tn0_w[k * 13 + c];
+#pragma unroll
+  for (int c = 0; c < 13; c++) a.g_tn0_w[k * 13 + c] = g0[c] + dh * e[c];
 }
 
 }  // namespace d3g
