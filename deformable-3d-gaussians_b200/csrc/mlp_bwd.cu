@@ -338,8 +338,8 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
 // ================================================================================================
 // Kernel 2: weight gradients.  One work item = one (A image set, B image set) GEMM over all tiles.
 // ================================================================================================
-constexpr int kWgStages = 4;
-constexpr uint32_t kWgABytes = 16384;                 // 32 points x 128 features
+constexpr int kWgStages = 3;
+constexpr uint32_t kWgABytes = 32768;                 // 32 points x 256 features (both halves of the outputs)
 constexpr uint32_t kWgBBytes = 32768;                 // 32 points x up to 256 features
 constexpr uint32_t kWgStageBytes = kWgABytes + kWgBBytes;
 constexpr int kWgThreads = 192;                       // warp 0 producer, 1 MMA, 2..5 epilogue
@@ -399,7 +399,9 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   volatile int* abort_flag = a.abort_flag;
-  const int pair = blockIdx.x >> 1, pairs = gridDim.x >> 1, half = blockIdx.x & 1;
+  // every CTA owns all 256 outputs of its tile range (two M=128 accumulators = all 512 TMEM columns): the B stage
+  // is then read once per point instead of once per CTA of a pair (a third less L2->SM traffic)
+  const int pair = blockIdx.x, pairs = gridDim.x;
 
   if (tid == 0) {
     for (int i = 0; i < kWgStages; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 5); }  // MMA commit + 4 warps
@@ -429,7 +431,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
         wg_segment(a, pair, pairs, it, base, total, t0, t1);
         base += (int64_t)w.cost * a.tiles;
         for (int tile = t0; ok && tile < t1; tile++) {
-          const uint8_t* pa = w.a_img + (size_t)tile * kHBytes + half * kWgABytes;
+          const uint8_t* pa = w.a_img + (size_t)tile * kHBytes;
           const uint8_t* pb = w.b_img + (size_t)tile * w.b_tile_bytes;
           for (int ch = 0; ch < 4; ch++) {
             if (!mbar_wait(&empty[s], ph ^ 1, abort_flag)) { ok = false; break; }
@@ -471,8 +473,9 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
 #pragma unroll
             for (int k8 = 0; k8 < 4; k8++) {
               if (a.dbg & 2) break;
-              const uint64_t ad = make_smem_desc_mn(sa + k8 * 1024);
-              umma_tf32_ss(tmem_base, ad, make_smem_desc_mn(sb + k8 * 1024), idesc, first ? 0u : 1u);
+              const uint64_t bd = make_smem_desc_mn(sb + k8 * 1024);
+              umma_tf32_ss(tmem_base, make_smem_desc_mn(sa + k8 * 1024), bd, idesc, first ? 0u : 1u);
+              umma_tf32_ss(tmem_base + 256, make_smem_desc_mn(sa + 16384 + k8 * 1024), bd, idesc, first ? 0u : 1u);
               first = 0;
             }
             if (a.dbg & 8) mbar_arrive(&empty[s]); else umma_commit(&empty[s]);
@@ -485,8 +488,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
   } else {
     // ================= epilogue: TMEM -> reductions into the gradient tensors =================
     const int q = warp & 3;  // TMEM lane quarter this warp may access
-    const int o = half * 128 + q * 32 + lane;
-    const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+    const uint32_t lane_addr0 = tmem_base + ((uint32_t)(q * 32) << 16);
     uint32_t f_ph = 0;
     bool ok = true;
     int64_t base = 0;
@@ -502,19 +504,23 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
       wg_segment(a, pair, pairs, it, base, total, t0, t1);
       base += (int64_t)w.cost * a.tiles;
       if (t0 >= t1) continue;
-      float bsum = 0.f;
+      float bsum = 0.f, bsum1 = 0.f;
       for (int tile = t0; ok && tile < t1; tile++) {
         for (int ch = 0; ch < 4; ch++) {
           if (!mbar_wait(&full[s], ph, abort_flag)) { ok = false; break; }
           if (w.bias) {
             const uint8_t* sa = sStage + (size_t)s * kWgStageBytes + f_off;
-            float acc0 = 0.f, acc1 = 0.f;
+            float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
 #pragma unroll
             for (int p = 0; p < 32; p += 2) {
-              acc0 += *(const float*)(sa + p * 128 + ((f_chunk ^ (p & 3)) << 5));
-              acc1 += *(const float*)(sa + (p + 1) * 128 + ((f_chunk ^ ((p + 1) & 3)) << 5));
+              const uint32_t o0 = p * 128 + ((f_chunk ^ (p & 3)) << 5), o1 = (p + 1) * 128 + ((f_chunk ^ ((p + 1) & 3)) << 5);
+              acc0 += *(const float*)(sa + o0);
+              acc1 += *(const float*)(sa + o1);
+              acc2 += *(const float*)(sa + 16384 + o0);   // feature f + 128
+              acc3 += *(const float*)(sa + 16384 + o1);
             }
             bsum += acc0 + acc1;
+            bsum1 += acc2 + acc3;
           }
           __syncwarp();
           if (lane == 0) mbar_arrive(&empty[s]);
@@ -525,6 +531,9 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
       if (!mbar_wait(acc_full, f_ph, abort_flag)) { ok = false; break; }
       f_ph ^= 1;
       tc_fence_after();
+      for (int hh = 0; hh < 2; hh++) {
+      const int o = hh * 128 + q * 32 + lane;
+      const uint32_t lane_addr = lane_addr0 + hh * 256;
       for (int c0 = 0; c0 < w.N; c0 += 32) {
         uint32_t v[32];
         tmem_ld32(lane_addr + c0, v);
@@ -551,10 +560,10 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
             if (a.head_dw[j]) atomicAdd(a.head_dw[j] + o, __uint_as_float(v[j]));
         }
       }
+      }
       if (w.bias) {
-        const int ob = half * 128 + f;
-        if (w.db) atomicAdd(w.db + ob, bsum);
-        if (w.db_fresh) atomicAdd(w.db_fresh + ob, bsum);
+        if (w.db) { atomicAdd(w.db + f, bsum); atomicAdd(w.db + 128 + f, bsum1); }
+        if (w.db_fresh) { atomicAdd(w.db_fresh + f, bsum); atomicAdd(w.db_fresh + 128 + f, bsum1); }
       }
       tc_fence_before();
       __syncwarp();
@@ -704,14 +713,14 @@ extern "C" int d3g_mlp_backward(const d3g_mlp_config* cfg, const void* packed, c
       w.db_fresh = (bias && l == 0) ? db_fresh : ((bias && l == 5) ? db_fresh + 256 : nullptr);
     };
     for (int l = 7; l >= 1; l--)
-      trunk(l, ws.h_img + (size_t)(l - 1) * layer_stride, kHBytes, 256, 1, l == 5 ? pe_dim : 0, 256, 48);
-    trunk(0, ws.pe_img, kPeBytes, 96, 1, 0, pe_dim, 28);
-    trunk(5, ws.pe_img, kPeBytes, 96, 0, 0, pe_dim, 28);
+      trunk(l, ws.h_img + (size_t)(l - 1) * layer_stride, kHBytes, 256, 1, l == 5 ? pe_dim : 0, 256, 64);
+    trunk(0, ws.pe_img, kPeBytes, 96, 1, 0, pe_dim, 44);
+    trunk(5, ws.pe_img, kPeBytes, 96, 0, 0, pe_dim, 44);
     {
       WgItem& w = a.items[n++];
       w.a_img = ws.h_img + (size_t)7 * layer_stride;
       w.b_img = ws.dout_img; w.b_tile_bytes = kDoutBytes; w.b_chunk_bytes = 4096; w.N = 32;
-      w.bias = 0; w.kind = 1; w.cost = 20;
+      w.bias = 0; w.kind = 1; w.cost = 36;
     }
     a.n_items = n;
     d3g_mlp_params gp;  // the gradient struct has the same layout; reuse head_map on it
@@ -720,8 +729,7 @@ extern "C" int d3g_mlp_backward(const d3g_mlp_config* cfg, const void* packed, c
     for (int j = 0; j < 16; j++) a.head_dw[j] = hm.w[j] ? (float*)hm.w[j] + (size_t)hm.r[j] * 256 : nullptr;
     size_t smem = (size_t)kWgStages * kWgStageBytes + 2048 + 256 + 1024;
     D3G_CUDA_TRY(cudaFuncSetAttribute(mlp_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int grid = num_sms() & ~1;
-    if (grid < 2) grid = 2;
+    int grid = num_sms();
     { ProfScope _p(PROF_MLP_WGRAD, stream);
     mlp_wgrad_kernel<<<grid, kWgThreads, smem, stream>>>(a);
     D3G_LAUNCH_CHECK(0, stream); }

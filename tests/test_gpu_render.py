@@ -92,11 +92,36 @@ def test_render_matches_oracle_through_public_api():
     cfg = ro.make_cfg(H, W, math.tan(camc.FoVx * 0.5), math.tan(camc.FoVy * 0.5), np.zeros(3), 1.0,
                       camc.world_view_transform.numpy(), camc.full_proj_transform.numpy(),
                       camc.camera_center.numpy(), 3, 16, 2, np.float32)
-    f = ro.forward(cfg, (gc.get_xyz + d_xyz).numpy(), gc.get_features.numpy(), None, gc.get_opacity.numpy(),
-                   (gc.get_scaling + d_scale).numpy(), (gc.get_rotation + d_rot).numpy(), None)
-    assert (out["radii"].cpu().numpy() != f["radii"]).sum() <= 1
-    assert np.abs(out["render"].detach().cpu().numpy() - f["color"]).max() <= 1e-4
-    assert np.abs(out["depth"].detach().cpu().numpy() - f["depth"]).max() <= 1e-4
+    # The oracle gets the activated tensors exactly as render()'s fused activation kernel hands them to the rasterizer
+    # (as smoke() does), after checking them against the torch-CPU activations.  Feeding it torch-CPU activations
+    # directly made this test flaky (~10 % of sessions): exp / sigmoid / normalize differ from the GPU's by an ulp
+    # here and there — and torch's vectorised CPU kernels not even reproducibly, depending on how the intra-op threads
+    # split the array — which is enough to flip an `alpha < 1/255` or `T < 1e-4` decision at a pixel (1e-3 jumps).
+    with torch.no_grad():
+        means, opac, scales, rots = pkg("renderer")._PrepareGaussians.apply(
+            g._xyz, deltas[0].detach(), g._scaling, deltas[2].detach(), g._rotation, deltas[1].detach(), g._opacity, False)
+    means, opac, scales, rots = [t.cpu() for t in (means, opac, scales, rots)]
+    for got, want in ((means, gc.get_xyz + d_xyz), (opac, gc.get_opacity), (scales, gc.get_scaling + d_scale),
+                      (rots, gc.get_rotation + d_rot)):
+        assert (got - want).abs().max() <= 2e-6 * want.abs().max()
+    f = ro.forward(cfg, means.numpy(), gc.get_features.numpy(), None, opac.numpy(), scales.numpy(), rots.numpy(), None)
+    assert np.array_equal(out["radii"].cpu().numpy(), f["radii"])
+
+    def diag():
+        st = pkg("rasterizer")._RasterizeGaussians.last_state
+        dd = np.abs(out["depth"].detach().cpu().numpy() - f["depth"])[0]
+        ys, xs = np.nonzero(dd > 1e-5)
+        with torch.no_grad():
+            again = pkg("renderer").render(cam, g, pipe, torch.zeros(3, device=dev), deltas[0], deltas[1], deltas[2], False)
+        pl = st.read(9, torch.int32, st.R).numpy().view(np.uint32) if st.R == f["R"] else None
+        return dict(R=(st.R, f["R"]), radii_mismatch=np.nonzero(out["radii"].cpu().numpy() != f["radii"])[0].tolist(),
+                    bad_px=len(ys), tiles=sorted(set(zip((ys // 16).tolist(), (xs // 16).tolist())))[:8],
+                    point_list_equal=None if pl is None else bool((pl == f["point_list"][:st.R]).all()),
+                    rerender_equal=bool(torch.equal(again["render"], out["render"])),
+                    rerender_vs_oracle=float(np.abs(again["render"].cpu().numpy() - f["color"]).max()))
+
+    assert np.abs(out["render"].detach().cpu().numpy() - f["color"]).max() <= 1e-4, diag()
+    assert np.abs(out["depth"].detach().cpu().numpy() - f["depth"]).max() <= 1e-4, diag()
     go = ro.backward(cfg, f, synth.image_cotangent(H, W).numpy(), None)
     assert _rel(grads[0], go["dL_dmeans3D"]) < 1e-3           # d(xyz) = d(means3D)
     assert _rel(grads[6], go["dL_dmeans3D"]) < 1e-3           # d(d_xyz) likewise
