@@ -164,6 +164,12 @@ typedef struct d3g_adam_tensor {
 int d3g_adam_step(int32_t n_tensors, const d3g_adam_tensor* tensors, float beta1, float beta2, float eps,
                   void* stream);
 
+/* `simple_knn._C.distCUDA2` (submodules/simple-knn/spatial.cu:15-26 -> SimpleKNN::knn, simple_knn.cu:185-221; caller
+ * scene/gaussian_model.py:105): mean_dist2[i] = mean of the three smallest squared distances from points[i] to the
+ * points at the OTHER indices (exact; FLT_MAX stands in for a missing neighbour when P < 4, as in the reference).
+ * points: [P,3] fp32 device, mean_dist2: [P] fp32 device.  Asynchronous on `stream`, no host round-trip, no allocation. */
+int d3g_knn_mean_dist2(int32_t P, const float* points, float* mean_dist2, void* stream);
+
 /* Upstream `markVisible` (never called by the reference; provided for API completeness).
  * present[i] = 1 iff view-space z > 0.2. */
 int d3g_mark_visible(int32_t N, const float* means3D, const float* viewmatrix, uint8_t* present,

@@ -1,0 +1,76 @@
+"""GPU: `simple_knn.distCUDA2` mirror (csrc/knn.cu through the C ABI) — bit-exact against the CPU restatement and
+against the UNMODIFIED reference kernel compiled into oracle/_ref/libsimple_knn_ref.so (built from
+/root/reference/submodules/simple-knn/simple_knn.cu in the build container; it travels with the snapshot)."""
+import importlib
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import knn_oracle
+
+pytestmark = pytest.mark.gpu
+knn = importlib.import_module("deformable-3d-gaussians_b200.simple_knn")
+
+
+def _clouds():
+    g = torch.Generator().manual_seed(0)
+    yield "uniform", (torch.rand(20000, 3, generator=g) * 2.6 - 1.3)          # scene/dataset_readers.py:286-290
+    yield "blob", (0.45 * torch.randn(5000, 3, generator=g)).clamp(-1.3, 1.3)
+    dup = torch.rand(3000, 3, generator=g)
+    dup[1000:2000] = dup[:1000]                                                # exact duplicates -> distance 0
+    yield "duplicates", dup
+    yield "grid", torch.stack(torch.meshgrid(*[torch.arange(12.0)] * 3, indexing="ij"), -1).reshape(-1, 3)  # ties
+    yield "tiny", torch.rand(5, 3, generator=g)
+    yield "ragged", torch.rand(1025, 3, generator=g) * 100.0                   # one past a shared-memory tile
+
+
+@pytest.mark.parametrize("name,pts", list(_clouds()), ids=[n for n, _ in _clouds()])
+def test_bit_exact_vs_oracle(name, pts):
+    got = knn.distCUDA2(pts.cuda()).cpu().numpy()
+    want = knn_oracle.mean_dist2(pts.numpy())
+    assert got.dtype == np.float32 and got.shape == want.shape
+    assert np.array_equal(got, want), "max abs diff %g" % np.abs(got - want).max()
+
+
+@pytest.mark.parametrize("name,pts", list(_clouds()), ids=[n for n, _ in _clouds()])
+def test_bit_exact_vs_compiled_reference(name, pts):
+    if not os.path.exists(knn_oracle.REF_SO):
+        pytest.skip("oracle/_ref/libsimple_knn_ref.so was not built (no /root/reference at build time)")
+    if pts.shape[0] < 4:
+        pytest.skip("reference reads uninitialised boxes below 4 points")
+    p = pts.cuda()
+    ref = knn_oracle.reference_mean_dist2(p).cpu().numpy()
+    got = knn.distCUDA2(p).cpu().numpy()
+    assert np.array_equal(got, ref), "max abs diff %g" % np.abs(got - ref).max()
+
+
+def test_full_size_against_reference_and_properties():
+    g = torch.Generator().manual_seed(1)
+    pts = (torch.rand(100000, 3, generator=g) * 2.6 - 1.3).cuda()            # C2 size, reference's random init
+    got = knn.distCUDA2(pts)
+    assert torch.isfinite(got).all() and (got > 0).all()
+    perm = torch.randperm(pts.size(0), generator=g).cuda()
+    assert torch.equal(knn.distCUDA2(pts[perm]), got[perm])                   # order-independent
+    if os.path.exists(knn_oracle.REF_SO):
+        assert torch.equal(got, knn_oracle.reference_mean_dist2(pts))
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev[0].record(); knn.distCUDA2(pts); ev[1].record(); torch.cuda.synchronize()
+    t_ours = ev[0].elapsed_time(ev[1])
+    msg = "distCUDA2 100k points: ours %.3f ms" % t_ours
+    if os.path.exists(knn_oracle.REF_SO):
+        import time
+        knn_oracle.reference_mean_dist2(pts)
+        t0 = time.perf_counter(); knn_oracle.reference_mean_dist2(pts); msg += ", reference %.3f ms (host clock, it syncs)" % ((time.perf_counter() - t0) * 1e3)
+    print(msg)
+    os.makedirs("gpurun_out", exist_ok=True)
+    open("gpurun_out/knn_timing.txt", "w").write(msg + "\n")
+
+
+def test_argument_errors():
+    with pytest.raises(RuntimeError):
+        knn.distCUDA2(torch.zeros(4, 3))
+    with pytest.raises(RuntimeError):
+        knn.distCUDA2(torch.zeros(4, 2, device="cuda"))
+    assert knn.distCUDA2(torch.zeros(0, 3, device="cuda")).shape == (0,)
