@@ -10,7 +10,11 @@ import torch
 from . import _lib
 
 
-def distCUDA2(points):
+GRID_MIN_POINTS = 4096   # below this the single all-pairs launch is as fast and needs no workspace
+
+
+def distCUDA2(points, method=None):
+    """method: None (by size), 'pairs' (all pairs through shared memory) or 'grid' (uniform-grid search); same result."""
     if not isinstance(points, torch.Tensor) or not points.is_cuda:
         raise RuntimeError("distCUDA2: points must be a CUDA tensor")
     if points.dim() != 2 or points.size(1) != 3:
@@ -22,5 +26,17 @@ def distCUDA2(points):
     means = torch.zeros(P, dtype=torch.float32, device=pts.device)   # reference: torch::full({P}, 0.0)
     with torch.cuda.device(pts.device):
         stream = torch.cuda.current_stream().cuda_stream
-        _lib.check(_lib.load().d3g_knn_mean_dist2(C.c_int32(P), _lib.ptr(pts), _lib.ptr(means), C.c_void_p(stream)))
+        lib = _lib.load()
+        if method is None:
+            method = "grid" if P >= GRID_MIN_POINTS else "pairs"
+        if method == "pairs":
+            _lib.check(lib.d3g_knn_mean_dist2(C.c_int32(P), _lib.ptr(pts), _lib.ptr(means), C.c_void_p(stream)))
+        elif method == "grid":
+            nbytes = C.c_size_t(0)
+            _lib.check(lib.d3g_knn_workspace_bytes(C.c_int32(P), C.byref(nbytes)))
+            ws = torch.empty(nbytes.value, dtype=torch.uint8, device=pts.device)
+            _lib.check(lib.d3g_knn_mean_dist2_grid(C.c_int32(P), _lib.ptr(pts), _lib.ptr(means), _lib.ptr(ws),
+                                                   C.c_size_t(nbytes.value), C.c_void_p(stream)))
+        else:
+            raise ValueError("distCUDA2: method must be None, 'pairs' or 'grid'")
     return means

@@ -169,6 +169,12 @@ int d3g_adam_step(int32_t n_tensors, const d3g_adam_tensor* tensors, float beta1
  * points at the OTHER indices (exact; FLT_MAX stands in for a missing neighbour when P < 4, as in the reference).
  * points: [P,3] fp32 device, mean_dist2: [P] fp32 device.  Asynchronous on `stream`, no host round-trip, no allocation. */
 int d3g_knn_mean_dist2(int32_t P, const float* points, float* mean_dist2, void* stream);
+/* The same result (bit for bit) for large clouds: exact search over a uniform grid built on the device (bounding box,
+ * counting sort by cell, shell-by-shell query) instead of all P^2 pairs.  workspace: d3g_knn_workspace_bytes(P) bytes
+ * of device memory, contents irrelevant on entry.  Asynchronous on `stream`, no host round-trip. */
+int d3g_knn_workspace_bytes(int32_t P, size_t* bytes);
+int d3g_knn_mean_dist2_grid(int32_t P, const float* points, float* mean_dist2, void* workspace,
+                            size_t workspace_bytes, void* stream);
 
 /* Upstream `markVisible` (never called by the reference; provided for API completeness).
  * present[i] = 1 iff view-space z > 0.2. */

@@ -26,9 +26,24 @@ def _clouds():
     yield "ragged", torch.rand(1025, 3, generator=g) * 100.0                   # one past a shared-memory tile
 
 
-@pytest.mark.parametrize("name,pts", list(_clouds()), ids=[n for n, _ in _clouds()])
-def test_bit_exact_vs_oracle(name, pts):
-    got = knn.distCUDA2(pts.cuda()).cpu().numpy()
+def _extra_clouds():
+    g = torch.Generator().manual_seed(5)
+    flat = torch.rand(40000, 3, generator=g); flat[:, 2] = 0.25                # planar: zero extent along z
+    yield "flat", flat
+    yield "line", torch.cat([torch.rand(3000, 1, generator=g), torch.zeros(3000, 2)], 1)
+    far = torch.rand(6000, 3, generator=g) * 0.01; far[0] = torch.tensor([50.0, -80.0, 3.0])   # one far outlier
+    yield "outlier", far
+    yield "offset", torch.rand(8000, 3, generator=g) + 1000.0                  # far from the origin: coarse ulps
+    yield "same", torch.ones(300, 3)                                            # all points coincide
+
+
+ALL = list(_clouds()) + list(_extra_clouds())
+
+
+@pytest.mark.parametrize("method", ["pairs", "grid"])
+@pytest.mark.parametrize("name,pts", ALL, ids=[n for n, _ in ALL])
+def test_bit_exact_vs_oracle(name, pts, method):
+    got = knn.distCUDA2(pts.cuda(), method=method).cpu().numpy()
     want = knn_oracle.mean_dist2(pts.numpy())
     assert got.dtype == np.float32 and got.shape == want.shape
     assert np.array_equal(got, want), "max abs diff %g" % np.abs(got - want).max()
@@ -42,7 +57,7 @@ def test_bit_exact_vs_compiled_reference(name, pts):
         pytest.skip("reference reads uninitialised boxes below 4 points")
     p = pts.cuda()
     ref = knn_oracle.reference_mean_dist2(p).cpu().numpy()
-    got = knn.distCUDA2(p).cpu().numpy()
+    got = knn.distCUDA2(p, method="grid").cpu().numpy()
     assert np.array_equal(got, ref), "max abs diff %g" % np.abs(got - ref).max()
 
 
@@ -50,6 +65,7 @@ def test_full_size_against_reference_and_properties():
     g = torch.Generator().manual_seed(1)
     pts = (torch.rand(100000, 3, generator=g) * 2.6 - 1.3).cuda()            # C2 size, reference's random init
     got = knn.distCUDA2(pts)
+    assert torch.equal(got, knn.distCUDA2(pts, method="pairs"))               # grid (default at this size) == all pairs
     assert torch.isfinite(got).all() and (got > 0).all()
     perm = torch.randperm(pts.size(0), generator=g).cuda()
     assert torch.equal(knn.distCUDA2(pts[perm]), got[perm])                   # order-independent
