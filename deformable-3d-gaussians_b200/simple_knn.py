@@ -40,3 +40,8 @@ def distCUDA2(points, method=None):
         else:
             raise ValueError("distCUDA2: method must be None, 'pairs' or 'grid'")
     return means
+
+
+import sys as _sys
+
+_C = _sys.modules[__name__]   # `from simple_knn._C import distCUDA2` works when this module is registered as simple_knn
