@@ -102,13 +102,21 @@ __global__ void __launch_bounds__(256) knn_bbox_kernel(int P, const float* __res
       const float v = pts[3 * (size_t)i + c];
       lo[c] = fminf(lo[c], v); hi[c] = fmaxf(hi[c], v);
     }
+  __shared__ float red[2][3][8];
 #pragma unroll
   for (int c = 0; c < 3; c++) {
     for (int o = 16; o; o >>= 1) {
       lo[c] = fminf(lo[c], __shfl_xor_sync(0xffffffffu, lo[c], o));
       hi[c] = fmaxf(hi[c], __shfl_xor_sync(0xffffffffu, hi[c], o));
     }
-    if ((threadIdx.x & 31) == 0) { atomicMin(&bbox[c], knn_enc(lo[c])); atomicMax(&bbox[3 + c], knn_enc(hi[c])); }
+    if ((threadIdx.x & 31) == 0) { red[0][c][threadIdx.x >> 5] = lo[c]; red[1][c][threadIdx.x >> 5] = hi[c]; }
+  }
+  __syncthreads();
+  if (threadIdx.x < 6) {           // six atomics per CTA (one per bound), not six per warp
+    const int which = threadIdx.x / 3, c = threadIdx.x % 3;
+    float v = red[which][c][0];
+    for (int w = 1; w < 8; w++) v = which ? fmaxf(v, red[1][c][w]) : fminf(v, red[0][c][w]);
+    if (which) atomicMax(&bbox[3 + c], knn_enc(v)); else atomicMin(&bbox[c], knn_enc(v));
   }
 }
 
@@ -265,7 +273,7 @@ extern "C" int d3g_knn_mean_dist2_grid(int32_t P, const float* points, float* me
   cudaMemsetAsync(bbox + 3, 0x00, 3 * sizeof(uint32_t), stream);    // encoded maxima at the smallest
   cudaMemsetAsync(counts, 0, (size_t)(L.cell_cap + 1) * sizeof(uint32_t), stream);
   const int nb = (P + 255) / 256;
-  knn_bbox_kernel<<<min(nb, 148 * 8), 256, 0, stream>>>(P, points, bbox);
+  knn_bbox_kernel<<<min(nb, 148 * 4), 256, 0, stream>>>(P, points, bbox);
   knn_plan_kernel<<<1, 1, 0, stream>>>(P, L.cell_cap, bbox, plan);
   knn_count_kernel<<<nb, 256, 0, stream>>>(P, points, plan, counts, cell_of, rank_of);
   size_t cub_bytes = L.cub_bytes;
