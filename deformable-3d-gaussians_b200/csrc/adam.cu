@@ -18,7 +18,7 @@ struct AdamSeg {
   float* p; const float* g; float* m; float* v;
   int64_t n;
   float step_size;      // lr / (1 - beta1^t)
-  float inv_bc2_sqrt;   // 1 / sqrt(1 - beta2^t)
+  float bc2_sqrt;       // sqrt(1 - beta2^t)
   float weight_decay;
   int first_block;      // prefix sum of CTAs
 };
@@ -34,7 +34,7 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
   if (s.weight_decay != 0.f) g = fmaf(s.weight_decay, p, g);
   m = m + a.om_beta1 * (g - m);
   v = v * b2 + a.om_beta2 * g * g;
-  const float denom = sqrtf(v) * s.inv_bc2_sqrt + eps;
+  const float denom = sqrtf(v) / s.bc2_sqrt + eps;   // torch divides (exp_avg_sq.sqrt() / bias_correction2_sqrt)
   p = p - s.step_size * (m / denom);
 }
 
@@ -72,12 +72,15 @@ adam_kernel(const __grid_constant__ AdamArgs a) {
 
 using namespace d3g;
 
-extern "C" int d3g_adam_step(int32_t n_tensors, const d3g_adam_tensor* t, float beta1, float beta2, float eps,
+extern "C" int d3g_adam_step(int32_t n_tensors, const d3g_adam_tensor* t, double beta1_d, double beta2_d, double eps_d,
                              void* stream_) {
   if (n_tensors < 0 || (n_tensors > 0 && !t)) return set_err(D3G_ERR_INVALID, "bad adam arguments");
   cudaStream_t stream = (cudaStream_t)stream_;
-  // the caller's betas are Python doubles rounded to float on the way in; recover the decimal value torch used
-  const double beta1_d = round((double)beta1 * 1e7) / 1e7, beta2_d = round((double)beta2 * 1e7) / 1e7;
+  // betas / eps cross the ABI as the Python doubles torch itself uses: 1 - beta and the bias corrections are taken
+  // from them in double, like torch.optim.Adam's scalar path
+  if (!(beta1_d >= 0.0 && beta1_d < 1.0) || !(beta2_d >= 0.0 && beta2_d < 1.0))
+    return set_err(D3G_ERR_INVALID, "adam: betas must lie in [0, 1)");
+  const float beta1 = (float)beta1_d, beta2 = (float)beta2_d, eps = (float)eps_d;
   int done = 0;
   while (done < n_tensors) {   // more than 48 tensors: several launches
     AdamArgs a;
@@ -92,7 +95,7 @@ extern "C" int d3g_adam_step(int32_t n_tensors, const d3g_adam_tensor* t, float 
       s.p = x.param; s.g = x.grad; s.m = x.exp_avg; s.v = x.exp_avg_sq; s.n = x.numel;
       const double bc1 = 1.0 - pow(beta1_d, (double)x.step), bc2 = 1.0 - pow(beta2_d, (double)x.step);
       s.step_size = (float)((double)x.lr / bc1);
-      s.inv_bc2_sqrt = (float)(1.0 / sqrt(bc2));
+      s.bc2_sqrt = (float)sqrt(bc2);
       s.weight_decay = x.weight_decay;
       s.first_block = blocks;
       const int64_t nb = (x.numel + kAdamPerBlock - 1) / kAdamPerBlock;

@@ -22,7 +22,7 @@ constexpr int kSW = kTW + 2 * kHalo, kSH = kTH + 2 * kHalo;  // 42 x 26 staged h
 constexpr int kLThreads = 256;
 
 __constant__ float c_win[11];
-static bool g_win_ready = false;
+static bool g_win_ready[64] = {};   // per device: constant memory is a per-device object
 
 // utils/loss_utils.py:31-33: exp(-(x - 5)^2 / (2 * 1.5^2)) as Python floats, stored as float32, divided by
 // their float32 sum.
@@ -242,11 +242,14 @@ int d3g_image_loss(int32_t C, int32_t H, int32_t W, const float* img, const floa
   if (C < 1 || H < 1 || W < 1) return set_err(D3G_ERR_INVALID, "bad image_loss shape");
   if (!img || !gt || !workspace || !out3) return set_err(D3G_ERR_INVALID, "NULL argument");
   cudaStream_t stream = (cudaStream_t)stream_;
-  if (!g_win_ready) {
+  int dev = 0;
+  D3G_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !g_win_ready[dev]) {
     float w[11];
     make_window(w);
-    D3G_CUDA_TRY(cudaMemcpyToSymbol(c_win, w, sizeof(w)));
-    g_win_ready = true;
+    D3G_CUDA_TRY(cudaMemcpyToSymbolAsync(c_win, w, sizeof(w), 0, cudaMemcpyHostToDevice, stream));
+    D3G_CUDA_TRY(cudaStreamSynchronize(stream));   // w is a stack buffer; once per device
+    if (dev >= 0 && dev < 64) g_win_ready[dev] = true;
   }
   const dim3 grid((W + kTW - 1) / kTW, (H + kTH - 1) / kTH, C);
   const size_t blocks = (size_t)grid.x * grid.y * grid.z;

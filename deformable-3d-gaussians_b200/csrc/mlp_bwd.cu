@@ -37,8 +37,9 @@ static_assert(BwdSmem::bars % 8 == 0, "barrier alignment");
 
 struct MlpBwdArgs {
   const uint8_t* wbwd;   // transposed weight stages
-  int64_t rows;
-  int tiles;
+  int64_t rows;          // points per time block
+  int tiles;             // all tiles (blocks * tpb)
+  int tpb;               // tiles per time block
   int is_6dof, heads;
   const uint32_t* mask;
   const float* heads_out;
@@ -224,8 +225,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
     uint32_t acc_ph = 0;
     bool ok = true;
     for (int tile = blockIdx.x; ok && tile < a.tiles; tile += gridDim.x) {
-      const int64_t grow = (int64_t)tile * kRows + row;
-      const bool live = grow < a.rows;
+      const int blk = tile / a.tpb;
+      const int64_t prow = (int64_t)(tile - blk * a.tpb) * kRows + row;
+      const bool live = prow < a.rows;
+      const int64_t grow = (int64_t)blk * a.rows + prow;   // row of the [blocks, rows, .] cotangents
       // ---- head cotangents -> shared A panel + HBM wgrad image; column sums for the head biases ----
       if (chalf == 0) {
         float o[16];
@@ -365,6 +368,7 @@ struct MlpWgradArgs {
   WgItem items[kWgItems];
   int n_items;
   int tiles;
+  int tpb;                // tiles per time block: db_fresh is kept per block ([blocks][2][256])
   float* head_dw[16];     // heads: gradient row pointers (NULL where the head is not evaluated)
   int* abort_flag;
 };
@@ -505,7 +509,17 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
       base += (int64_t)w.cost * a.tiles;
       if (t0 >= t1) continue;
       float bsum = 0.f, bsum1 = 0.f;
+      int cur_blk = t0 / a.tpb;
       for (int tile = t0; ok && tile < t1; tile++) {
+        if (w.bias && tile / a.tpb != cur_blk) {   // next time block: flush this block's bias sums
+          if (w.db) { atomicAdd(w.db + f, bsum); atomicAdd(w.db + 128 + f, bsum1); }
+          if (w.db_fresh) {
+            atomicAdd(w.db_fresh + (size_t)cur_blk * 512 + f, bsum);
+            atomicAdd(w.db_fresh + (size_t)cur_blk * 512 + 128 + f, bsum1);
+          }
+          bsum = bsum1 = 0.f;
+          cur_blk = tile / a.tpb;
+        }
         for (int ch = 0; ch < 4; ch++) {
           if (!mbar_wait(&full[s], ph, abort_flag)) { ok = false; break; }
           if (w.bias) {
@@ -563,7 +577,10 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
       }
       if (w.bias) {
         if (w.db) { atomicAdd(w.db + f, bsum); atomicAdd(w.db + 128 + f, bsum1); }
-        if (w.db_fresh) { atomicAdd(w.db_fresh + f, bsum); atomicAdd(w.db_fresh + 128 + f, bsum1); }
+        if (w.db_fresh) {
+          atomicAdd(w.db_fresh + (size_t)cur_blk * 512 + f, bsum);
+          atomicAdd(w.db_fresh + (size_t)cur_blk * 512 + 128 + f, bsum1);
+        }
       }
       tc_fence_before();
       __syncwarp();
@@ -576,113 +593,382 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
 }
 
 // ================================================================================================
-// Kernel 3: head-bias gradients, and the timenet backward when all rows share one time value.
+// Kernel 3: head-bias gradients, and the timenet backward of every time block whose rows share one time value.
 //   t-feature columns 63..92 of the pe block feed layer 0 and the skip layer, so with a shared t
-//   d tfeat[j] = sum_o db_0[o] W_0[o][63+j] + db_5[o] W_5[o][63+j]   (db = this call's bias gradients),
-//   then utils/time_utils.py:74-76 backwards: tfeat = W2 relu(W0t e + b0t) + b2.
+//   sum_rows d tfeat[j] = sum_o db_0[o] W_0[o][63+j] + db_5[o] W_5[o][63+j]   (db = this block's bias gradients),
+//   then utils/time_utils.py:74-76 backwards: tfeat = W2 relu(W0t e + b0t) + b2.  Everything behind tfeat is
+//   constant over the block, so the same sums give sum_rows dL/dt (dL_dt_blocks, nullable).
+//   One CTA per time block; parameter gradients are accumulated with atomics.
 // ================================================================================================
 struct MlpFinishArgs {
   const float* headb_acc;   // [16]
   float* head_db[16];       // gradient element pointers (NULL where absent)
   int is_blender;
-  const float* db_fresh;    // [2][256]
+  int per_row;              // plain call with per-row time values: when they differ, mlp_timenet_rows_kernel
+  const int* nonuniform;    // owns the timenet gradients and this kernel only does the head biases
+  const float* db_fresh;    // [blocks][2][256]
   const float* w0;          // linear.0.weight [256, pe_dim]
   const float* w5;          // linear.5.weight [256, pe_dim+256]
   int pe_dim;
-  const float* t;           // shared time value
-  const float* thidden;     // [256] post-ReLU timenet hidden
+  const float* t;           // time value of block b at t[b * t_step]
+  int t_step;
+  const float* thidden;     // [blocks][256] post-ReLU timenet hidden
+  const float* tn0_w;       // timenet.0.weight [256,13]
   const float* tn2_w;       // timenet.2.weight [30,256]
   float* g_tn0_w; float* g_tn0_b; float* g_tn2_w; float* g_tn2_b;
+  float* dL_dt_blocks;      // [blocks] or NULL
 };
 
 __global__ void __launch_bounds__(256) mlp_finish_kernel(MlpFinishArgs a) {
   __shared__ float dtf[32];
-  __shared__ float e[16];
-  const int tid = threadIdx.x;
-  if (tid < 16 && a.head_db[tid]) *a.head_db[tid] += a.headb_acc[tid];
-  if (!a.is_blender) return;
-  if (tid < 13) {
-    float tv = a.t[0];
-    float v = tv;
-    if (tid > 0) {
-      int f = (tid - 1) >> 1;
-      float arg = tv * (float)(1 << f);
+  __shared__ float e[32];
+  __shared__ float de[16];
+  const int tid = threadIdx.x, blk = blockIdx.x;
+  if (blk == 0 && tid < 16 && a.head_db[tid]) atomicAdd(a.head_db[tid], a.headb_acc[tid]);
+  if (a.per_row && *a.nonuniform) return;   // the per-row kernels handle the time path
+  if (!a.is_blender && !a.dL_dt_blocks) return;
+  const int L = a.is_blender ? 6 : 10, t_dim = a.is_blender ? 30 : 21;
+  if (tid < 32) {
+    const float tv = a.t[(size_t)blk * a.t_step];
+    float v = 0.f;
+    if (tid == 0) v = tv;
+    else if (tid < 1 + 2 * L) {
+      const int f = (tid - 1) >> 1;
+      const float arg = tv * (float)(1 << f);
       v = ((tid - 1) & 1) ? cosf(arg) : sinf(arg);
     }
     e[tid] = v;
   }
+  if (tid < 16) de[tid] = 0.f;
   {
     const int warp = tid >> 5, lane = tid & 31;
-    // (independent loads issued together: this single-CTA kernel is pure latency)
-#pragma unroll
-    for (int j = warp; j < 30; j += 8) {
+    const float* dbf = a.db_fresh + (size_t)blk * 512;
+    for (int j = warp; j < t_dim; j += 8) {
       float acc = 0.f;
 #pragma unroll
       for (int o = lane; o < 256; o += 32)
-        acc += a.db_fresh[o] * a.w0[(size_t)o * a.pe_dim + 63 + j] +
-               a.db_fresh[256 + o] * a.w5[(size_t)o * (a.pe_dim + 256) + 63 + j];
+        acc += dbf[o] * a.w0[(size_t)o * a.pe_dim + 63 + j] + dbf[256 + o] * a.w5[(size_t)o * (a.pe_dim + 256) + 63 + j];
 #pragma unroll
       for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
       if (lane == 0) dtf[j] = acc;
     }
   }
   __syncthreads();
+  if (!a.is_blender) {
+    // tfeat = PE_10(t) itself: d/dt of [t, sin(2^f t), cos(2^f t)]
+    if (tid == 0) {
+      float dt = dtf[0];
+      for (int f = 0; f < L; f++) dt += (dtf[1 + 2 * f] * e[2 + 2 * f] - dtf[2 + 2 * f] * e[1 + 2 * f]) * (float)(1 << f);
+      a.dL_dt_blocks[blk] = dt;
+    }
+    return;
+  }
   // thread k owns hidden unit k
   const int k = tid;
-  const float hk = a.thidden[k];
+  const float hk = a.thidden[(size_t)blk * 256 + k];
   float dh = 0.f;
-  float gw[30], tw[30];
-#pragma unroll
-  for (int i = 0; i < 30; i++) { gw[i] = a.g_tn2_w[i * 256 + k]; tw[i] = a.tn2_w[i * 256 + k]; }
 #pragma unroll
   for (int i = 0; i < 30; i++) {
-    a.g_tn2_w[i * 256 + k] = gw[i] + dtf[i] * hk;
-    dh += tw[i] * dtf[i];
+    atomicAdd(&a.g_tn2_w[i * 256 + k], dtf[i] * hk);
+    dh += a.tn2_w[i * 256 + k] * dtf[i];
   }
-  if (k < 30) a.g_tn2_b[k] += dtf[k];
+  if (k < 30) atomicAdd(&a.g_tn2_b[k], dtf[k]);
   if (!(hk > 0.f)) dh = 0.f;
-  a.g_tn0_b[k] += dh;
-  float g0[13];
+  atomicAdd(&a.g_tn0_b[k], dh);
 #pragma unroll
-  for (int c = 0; c < 13; c++) g0[c] = a.g_tn0_w[k * 13 + c];
+  for (int c = 0; c < 13; c++) atomicAdd(&a.g_tn0_w[k * 13 + c], dh * e[c]);
+  if (a.dL_dt_blocks) {
 #pragma unroll
-  for (int c = 0; c < 13; c++) a.g_tn0_w[k * 13 + c] = g0[c] + dh * e[c];
+    for (int c = 0; c < 13; c++) {
+      float v = dh * a.tn0_w[k * 13 + c];
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+      if ((tid & 31) == 0) atomicAdd(&de[c], v);
+    }
+    __syncthreads();
+    if (tid == 0) {
+      float dt = de[0];
+      for (int f = 0; f < 6; f++) dt += (de[1 + 2 * f] * e[2 + 2 * f] - de[2 + 2 * f] * e[1 + 2 * f]) * (float)(1 << f);
+      a.dL_dt_blocks[blk] = dt;
+    }
+  }
+}
+
+// ================================================================================================
+// General backward of the input block (CUDA cores; only launched when a caller wants dL/dxyz or dL/dt, or when the
+// rows of a blender call carry different time values):
+//   dPE[p][c] = sum_o dZ_0[p][o] W_0[o][c] + dZ_5[p][o] W_5[o][c],  c < pe_dim        (mlp_dpe_kernel)
+//   dL/dxyz through [x, sin(2^f x), cos(2^f x)] (utils/time_utils.py:46-54)            (mlp_pe_bwd_kernel)
+//   per-row timenet backward 30 <- 256 <- 13 and dL/dt                                 (mlp_timenet_rows_kernel)
+// ================================================================================================
+struct MlpDpeArgs {
+  const uint8_t* dz0;   // dZ images of layer 0 and layer 5, [tiles] x 128 KB
+  const uint8_t* dz5;
+  const float* w0;      // [256, pe_dim]
+  const float* w5;      // [256, pe_dim + 256]
+  int pe_dim;
+  int tiles;
+  float* dpe;           // [tiles*128, 96]
+  int skip_if_uniform;  // nothing downstream needs dPE when the time values turned out equal
+  const int* nonuniform;
+};
+
+__global__ void __launch_bounds__(256) mlp_dpe_kernel(MlpDpeArgs a) {
+  __shared__ __align__(16) uint8_t sA[4 * 4096];   // 128 points x 32 features, raw wgrad-image blocks
+  __shared__ __align__(16) float sB[32 * 96];
+  if (a.skip_if_uniform && !*a.nonuniform) return;
+  const int tid = threadIdx.x, rg = tid >> 4, cgp = tid & 15;
+  for (int tile = blockIdx.x; tile < a.tiles; tile += gridDim.x) {
+    float acc[8][6];
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+#pragma unroll
+      for (int j = 0; j < 6; j++) acc[i][j] = 0.f;
+    for (int src = 0; src < 2; src++) {
+      const uint8_t* img = (src ? a.dz5 : a.dz0) + (size_t)tile * kHBytes;
+      const float* W = src ? a.w5 : a.w0;
+      const int ld = src ? a.pe_dim + 256 : a.pe_dim;
+      for (int kc = 0; kc < 8; kc++) {
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          const int idx = tid + i * 256;            // float4 index, 256 per 4 KB block
+          const int pc = idx >> 8, within = idx & 255;
+          ((float4*)sA)[idx] = *(const float4*)(img + ((size_t)pc * 8 + kc) * 4096 + (size_t)within * 16);
+        }
+        for (int idx = tid; idx < 32 * 96; idx += 256) {
+          const int k = idx / 96, c = idx - k * 96;
+          sB[idx] = c < a.pe_dim ? W[(size_t)(kc * 32 + k) * ld + c] : 0.f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k4 = 0; k4 < 8; k4++) {
+          float av[8][4];
+#pragma unroll
+          for (int i = 0; i < 8; i++) {
+            const int p = rg * 8 + i;
+            // img_off_mn inside the 32-feature panel: 32-byte chunk (k/8) ^ (p&3), 16-byte half (k%8)/4
+            const float4 v = *(const float4*)(sA + (p >> 5) * 4096 + (p & 31) * 128 + ((((k4 >> 1)) ^ (p & 3)) << 5) +
+                                              ((k4 & 1) << 4));
+            av[i][0] = v.x; av[i][1] = v.y; av[i][2] = v.z; av[i][3] = v.w;
+          }
+#pragma unroll
+          for (int kk = 0; kk < 4; kk++) {
+            const float* br = sB + (k4 * 4 + kk) * 96 + cgp * 6;
+            const float2 b0 = *(const float2*)br, b1 = *(const float2*)(br + 2), b2 = *(const float2*)(br + 4);
+            const float bv[6] = {b0.x, b0.y, b1.x, b1.y, b2.x, b2.y};
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+#pragma unroll
+              for (int j = 0; j < 6; j++) acc[i][j] = fmaf(av[i][kk], bv[j], acc[i][j]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      float* dst = a.dpe + ((size_t)tile * kRows + rg * 8 + i) * 96 + cgp * 6;
+#pragma unroll
+      for (int j = 0; j < 3; j++) *(float2*)(dst + 2 * j) = make_float2(acc[i][2 * j], acc[i][2 * j + 1]);
+    }
+  }
+}
+
+struct MlpPeBwdArgs {
+  const float* dpe;      // [tiles*128, 96]
+  const float* xyz;      // [rows,3]
+  int64_t rows;
+  int tpb, blocks;
+  float* dL_dxyz;        // [rows,3] (summed over the time blocks) or NULL
+  // not blender: tfeat = PE_10(t) -> per-row dL/dt straight from the pe cotangent (plain per-row call only)
+  float* dL_dt_rows;     // [rows] or NULL
+  const float* t; int64_t t_stride;
+};
+
+__global__ void __launch_bounds__(256) mlp_pe_bwd_kernel(MlpPeBwdArgs a) {
+  const int64_t total = (int64_t)a.blocks * a.rows;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int blk = (int)(i / a.rows);
+    const int64_t prow = i - (int64_t)blk * a.rows;
+    const float* g = a.dpe + ((size_t)blk * a.tpb * kRows + prow) * 96;
+    if (a.dL_dxyz) {
+      float out[3];
+#pragma unroll
+      for (int d = 0; d < 3; d++) {
+        const float x = a.xyz[3 * prow + d];
+        float acc = g[d];
+#pragma unroll
+        for (int f = 0; f < 10; f++) {
+          const float fr = (float)(1 << f);
+          float sn, cs;
+          sincosf(x * fr, &sn, &cs);
+          acc += (g[3 + 6 * f + d] * cs - g[3 + 6 * f + 3 + d] * sn) * fr;
+        }
+        out[d] = acc;
+      }
+      if (a.blocks > 1) {
+#pragma unroll
+        for (int d = 0; d < 3; d++) atomicAdd(a.dL_dxyz + 3 * prow + d, out[d]);
+      } else {
+#pragma unroll
+        for (int d = 0; d < 3; d++) a.dL_dxyz[3 * prow + d] = out[d];
+      }
+    }
+    if (a.dL_dt_rows) {
+      const float tv = a.t[prow * a.t_stride];
+      float dt = g[63];
+#pragma unroll
+      for (int f = 0; f < 10; f++) {
+        const float fr = (float)(1 << f);
+        float sn, cs;
+        sincosf(tv * fr, &sn, &cs);
+        dt += (g[64 + 2 * f] * cs - g[65 + 2 * f] * sn) * fr;
+      }
+      a.dL_dt_rows[prow] = dt;
+    }
+  }
+}
+
+// Per-row timenet backward (blender, plain call whose rows carry their own time value; scene/deform_model.py:260-273
+// accepts arbitrary [N,T], train_baseline.py:110-115 passes a materialised [N,1]).  Thread k owns hidden unit k and
+// keeps its slices of the four parameter gradients in registers over the CTA's rows; rows are processed 32 at a time.
+struct MlpTimenetRowsArgs {
+  const float* dpe;        // [rows(+pad), 96]; columns 63..92 = d tfeat
+  const float* t; int64_t t_stride;
+  int64_t rows;
+  const float* thidden;    // [rows,256], or [1,256] when the values turned out equal
+  const float* tn0_w;      // [256,13]
+  const float* tn2_w;      // [30,256]
+  float* g_tn0_w; float* g_tn0_b; float* g_tn2_w; float* g_tn2_b;
+  float* dL_dt_rows;       // [rows] or NULL
+  const int* nonuniform;
+};
+
+__global__ void __launch_bounds__(256) mlp_timenet_rows_kernel(MlpTimenetRowsArgs a) {
+  __shared__ float s_dtf[32][32];
+  __shared__ float s_e[32][16];
+  __shared__ float s_de[8][32][13];
+  const int nonuni = *a.nonuniform;
+  if (!nonuni && !a.dL_dt_rows) return;   // equal values and nobody wants per-row dL/dt: mlp_finish_kernel did it
+  const int k = threadIdx.x, warp = k >> 5, lane = k & 31;
+  float w2c[30], w0r[13], acc_w2[30], acc_w0[13], acc_b0 = 0.f;
+#pragma unroll
+  for (int i = 0; i < 30; i++) { w2c[i] = a.tn2_w[i * 256 + k]; acc_w2[i] = 0.f; }
+#pragma unroll
+  for (int c = 0; c < 13; c++) { w0r[c] = a.tn0_w[k * 13 + c]; acc_w0[c] = 0.f; }
+  float acc_b2 = 0.f;   // threads 0..29: sum of d tfeat[k]
+  const int64_t nbatch = (a.rows + 31) / 32;
+  for (int64_t bt = blockIdx.x; bt < nbatch; bt += gridDim.x) {
+    const int64_t r0 = bt * 32;
+    __syncthreads();
+    for (int idx = k; idx < 32 * 32; idx += 256) {
+      const int rr = idx >> 5, j = idx & 31;
+      const int64_t r = r0 + rr;
+      s_dtf[rr][j] = (r < a.rows && j < 30) ? a.dpe[(size_t)r * 96 + 63 + j] : 0.f;
+    }
+    for (int idx = k; idx < 32 * 13; idx += 256) {
+      const int rr = idx / 13, j = idx - rr * 13;
+      const int64_t r = r0 + rr;
+      float v = 0.f;
+      if (r < a.rows) {
+        const float tv = a.t[r * a.t_stride];
+        if (j == 0) v = tv;
+        else {
+          const int f = (j - 1) >> 1;
+          const float arg = tv * (float)(1 << f);
+          v = ((j - 1) & 1) ? cosf(arg) : sinf(arg);
+        }
+      }
+      s_e[rr][j] = v;
+    }
+    __syncthreads();
+    for (int rr = 0; rr < 32; rr++) {
+      const int64_t r = r0 + rr;
+      if (r >= a.rows) break;
+      const float hk = a.thidden[(nonuni ? (size_t)r * 256 : 0) + k];
+      float dh = 0.f;
+#pragma unroll
+      for (int i = 0; i < 30; i++) {
+        const float d = s_dtf[rr][i];
+        acc_w2[i] = fmaf(d, hk, acc_w2[i]);
+        dh = fmaf(w2c[i], d, dh);
+      }
+      if (!(hk > 0.f)) dh = 0.f;
+      acc_b0 += dh;
+#pragma unroll
+      for (int c = 0; c < 13; c++) acc_w0[c] = fmaf(dh, s_e[rr][c], acc_w0[c]);
+      if (a.dL_dt_rows) {
+#pragma unroll
+        for (int c = 0; c < 13; c++) {
+          float v = dh * w0r[c];
+#pragma unroll
+          for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+          if (lane == 0) s_de[warp][rr][c] = v;
+        }
+      }
+    }
+    if (k < 30) {
+#pragma unroll 4
+      for (int rr = 0; rr < 32; rr++) acc_b2 += s_dtf[rr][k];
+    }
+    if (a.dL_dt_rows) {
+      __syncthreads();
+      if (k < 32 && r0 + k < a.rows) {
+        float de[13];
+#pragma unroll
+        for (int c = 0; c < 13; c++) {
+          float v = 0.f;
+#pragma unroll
+          for (int w = 0; w < 8; w++) v += s_de[w][k][c];
+          de[c] = v;
+        }
+        float dt = de[0];
+#pragma unroll
+        for (int f = 0; f < 6; f++) dt += (de[1 + 2 * f] * s_e[k][2 + 2 * f] - de[2 + 2 * f] * s_e[k][1 + 2 * f]) * (float)(1 << f);
+        a.dL_dt_rows[r0 + k] = dt;
+      }
+    }
+  }
+  if (!nonuni) return;   // equal values: the parameter gradients came from mlp_finish_kernel's shortcut
+#pragma unroll
+  for (int i = 0; i < 30; i++) atomicAdd(&a.g_tn2_w[i * 256 + k], acc_w2[i]);
+  if (k < 30) atomicAdd(&a.g_tn2_b[k], acc_b2);
+  atomicAdd(&a.g_tn0_b[k], acc_b0);
+#pragma unroll
+  for (int c = 0; c < 13; c++) atomicAdd(&a.g_tn0_w[k * 13 + c], acc_w0[c]);
 }
 
 }  // namespace d3g
 
 using namespace d3g;
 
-extern "C" int d3g_mlp_backward(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp_params* p,
-                                int64_t rows, const float* xyz, const float* t, int64_t t_stride, void* workspace,
-                                const float* dL_dxyz_out, const float* dL_drot, const float* dL_dscale,
-                                const d3g_mlp_grads* g, float* dL_dxyz, float* dL_dt, void* stream_) {
+static int mlp_backward_impl(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp_params* p, int64_t n,
+                             int blocks, const float* xyz, const float* t, int64_t t_stride, void* workspace,
+                             const float* dL_dxyz_out, const float* dL_drot, const float* dL_dscale,
+                             const d3g_mlp_grads* g, float* dL_dxyz, float* dL_dt, cudaStream_t stream) {
   if (int e = check_cfg(cfg)) return e;
   if (!packed || !p || !workspace || !g) return set_err(D3G_ERR_INVALID, "NULL argument");
-  if (rows < 0 || (rows > 0 && (!xyz || !t))) return set_err(D3G_ERR_INVALID, "NULL tensor");
-  if (dL_dxyz || dL_dt)
-    return set_err(D3G_ERR_UNSUPPORTED,
-                   "gradients w.r.t. xyz / t are not implemented (every reference call site passes xyz.detach())");
-  if (cfg->is_blender && t_stride != 0 && rows > 1)
-    return set_err(D3G_ERR_UNSUPPORTED, "timenet backward with per-row time values is not implemented");
+  if (n < 0 || blocks < 1 || (n > 0 && (!xyz || !t))) return set_err(D3G_ERR_INVALID, "NULL tensor");
   for (int l = 0; l < 8; l++)
     if (!g->linear_w[l] || !g->linear_b[l]) return set_err(D3G_ERR_INVALID, "linear.%d gradient buffers missing", l);
   if (cfg->is_blender && (!g->timenet0_w || !g->timenet0_b || !g->timenet2_w || !g->timenet2_b))
     return set_err(D3G_ERR_INVALID, "timenet gradient buffers missing");
-  if (rows == 0) return 0;
-  cudaStream_t stream = (cudaStream_t)stream_;
-  MlpWs ws = mlp_ws_view(workspace, rows, true);
-  const int tiles = (int)((rows + kRows - 1) / kRows);
+  if (n == 0) return 0;
+  const MlpShape sh = mlp_shape(n, blocks);
+  MlpWs ws = mlp_ws_view(workspace, n, true, blocks);
+  const int tiles = sh.tiles;
   const int pe_dim = cfg->is_blender ? 93 : 84;
-  D3G_CUDA_TRY(cudaMemsetAsync(ws.scratch, 0, kScratchFloats * 4, stream));
+  const bool per_row = blocks == 1 && t_stride != 0 && n > 1;   // same rule as forward
+  D3G_CUDA_TRY(cudaMemsetAsync(ws.scratch, 0, ws.scratch_floats * 4, stream));
   float* headb_acc = ws.scratch;
   float* db_fresh = ws.scratch + 16;
+  int* nonuniform = ws.status + 1;
 
   // ---- kernel 1: input-gradient chain ----
   {
     MlpBwdArgs a;
     a.wbwd = (const uint8_t*)packed + kBwdOff;
-    a.rows = rows; a.tiles = tiles; a.is_6dof = cfg->is_6dof; a.heads = cfg->heads;
+    a.rows = n; a.tiles = tiles; a.tpb = sh.tpb; a.is_6dof = cfg->is_6dof; a.heads = cfg->heads;
     a.mask = ws.mask; a.heads_out = ws.heads_out;
     a.g_xyz = dL_dxyz_out;
     a.g_rot = (cfg->heads & 2) ? dL_drot : nullptr;
@@ -696,15 +982,18 @@ extern "C" int d3g_mlp_backward(const d3g_mlp_config* cfg, const void* packed, c
     D3G_LAUNCH_CHECK(0, stream); }
   }
   // ---- kernel 2: weight gradients ----
+  d3g_mlp_params gp;  // the gradient struct has the same layout; reuse head_map on it
+  memcpy(&gp, g, sizeof(gp));
+  HeadMap hm = head_map(*cfg, gp);
   {
     MlpWgradArgs a;
     memset(&a, 0, sizeof(a));
     { const char* e = getenv("D3G_WGRAD_DBG"); a.dbg = e ? atoi(e) : 0; }
-    a.tiles = tiles; a.abort_flag = ws.status;
+    a.tiles = tiles; a.tpb = sh.tpb; a.abort_flag = ws.status;
     const size_t layer_stride = (size_t)tiles * kHBytes;
-    int n = 0;
+    int nit = 0;
     auto trunk = [&](int l, const uint8_t* b_img, uint32_t b_tile, int N, int bias, int col0, int ncols, int cost) {
-      WgItem& w = a.items[n++];
+      WgItem& w = a.items[nit++];
       w.a_img = ws.dz_img + (size_t)l * layer_stride;
       w.b_img = b_img; w.b_tile_bytes = b_tile; w.b_chunk_bytes = (uint32_t)(N / 32) * 4096u; w.N = N;
       w.bias = bias; w.kind = 0; w.cost = cost;
@@ -717,15 +1006,12 @@ extern "C" int d3g_mlp_backward(const d3g_mlp_config* cfg, const void* packed, c
     trunk(0, ws.pe_img, kPeBytes, 96, 1, 0, pe_dim, 44);
     trunk(5, ws.pe_img, kPeBytes, 96, 0, 0, pe_dim, 44);
     {
-      WgItem& w = a.items[n++];
+      WgItem& w = a.items[nit++];
       w.a_img = ws.h_img + (size_t)7 * layer_stride;
       w.b_img = ws.dout_img; w.b_tile_bytes = kDoutBytes; w.b_chunk_bytes = 4096; w.N = 32;
       w.bias = 0; w.kind = 1; w.cost = 36;
     }
-    a.n_items = n;
-    d3g_mlp_params gp;  // the gradient struct has the same layout; reuse head_map on it
-    memcpy(&gp, g, sizeof(gp));
-    HeadMap hm = head_map(*cfg, gp);
+    a.n_items = nit;
     for (int j = 0; j < 16; j++) a.head_dw[j] = hm.w[j] ? (float*)hm.w[j] + (size_t)hm.r[j] * 256 : nullptr;
     size_t smem = (size_t)kWgStages * kWgStageBytes + 2048 + 256 + 1024;
     D3G_CUDA_TRY(cudaFuncSetAttribute(mlp_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -733,20 +1019,78 @@ extern "C" int d3g_mlp_backward(const d3g_mlp_config* cfg, const void* packed, c
     { ProfScope _p(PROF_MLP_WGRAD, stream);
     mlp_wgrad_kernel<<<grid, kWgThreads, smem, stream>>>(a);
     D3G_LAUNCH_CHECK(0, stream); }
-    // ---- kernel 3 ----
+  }
+  // ---- kernel 3: head biases + shared-t timenet backward (one CTA per time block) ----
+  {
     MlpFinishArgs f;
     memset(&f, 0, sizeof(f));
     f.headb_acc = headb_acc;
     for (int j = 0; j < 16; j++) f.head_db[j] = hm.b[j] ? (float*)hm.b[j] + hm.r[j] : nullptr;
-    f.is_blender = cfg->is_blender;
+    f.is_blender = cfg->is_blender; f.per_row = per_row ? 1 : 0; f.nonuniform = nonuniform;
     f.db_fresh = db_fresh; f.w0 = p->linear_w[0]; f.w5 = p->linear_w[5]; f.pe_dim = pe_dim;
-    f.t = t; f.thidden = ws.thidden; f.tn2_w = p->timenet2_w;
+    f.t = t; f.t_step = blocks > 1 ? 1 : 0; f.thidden = ws.thidden; f.tn0_w = p->timenet0_w; f.tn2_w = p->timenet2_w;
     f.g_tn0_w = g->timenet0_w; f.g_tn0_b = g->timenet0_b; f.g_tn2_w = g->timenet2_w; f.g_tn2_b = g->timenet2_b;
+    f.dL_dt_blocks = per_row ? nullptr : dL_dt;
     { ProfScope _p(PROF_MLP_FINISH, stream);
-    mlp_finish_kernel<<<1, 256, 0, stream>>>(f);
+    mlp_finish_kernel<<<blocks, 256, 0, stream>>>(f);
     D3G_LAUNCH_CHECK(0, stream); }
   }
+  // ---- general input-block backward: dL/dxyz, per-row dL/dt, per-row timenet ----
+  const bool want_dt_rows = per_row && dL_dt != nullptr;
+  const bool rows_timenet = per_row && cfg->is_blender;
+  if (dL_dxyz || want_dt_rows || rows_timenet) {
+    MlpDpeArgs d;
+    d.dz0 = ws.dz_img; d.dz5 = ws.dz_img + (size_t)5 * tiles * kHBytes;
+    d.w0 = p->linear_w[0]; d.w5 = p->linear_w[5]; d.pe_dim = pe_dim; d.tiles = tiles; d.dpe = ws.dpe;
+    d.skip_if_uniform = (!dL_dxyz && !want_dt_rows) ? 1 : 0; d.nonuniform = nonuniform;
+    { ProfScope _p(PROF_MLP_DPE, stream);
+    mlp_dpe_kernel<<<tiles < 4 * num_sms() ? tiles : 4 * num_sms(), 256, 0, stream>>>(d);
+    D3G_LAUNCH_CHECK(0, stream); }
+    const bool dt_from_pe = want_dt_rows && !cfg->is_blender;
+    if (dL_dxyz || dt_from_pe) {
+      if (dL_dxyz && blocks > 1) D3G_CUDA_TRY(cudaMemsetAsync(dL_dxyz, 0, (size_t)n * 3 * 4, stream));
+      MlpPeBwdArgs e;
+      e.dpe = ws.dpe; e.xyz = xyz; e.rows = n; e.tpb = sh.tpb; e.blocks = blocks; e.dL_dxyz = dL_dxyz;
+      e.dL_dt_rows = dt_from_pe ? dL_dt : nullptr; e.t = t; e.t_stride = t_stride;
+      const int64_t total = (int64_t)blocks * n;
+      int64_t gb = (total + 255) / 256;
+      if (gb > 16 * (int64_t)num_sms()) gb = 16 * (int64_t)num_sms();
+      { ProfScope _p(PROF_MLP_DPE, stream);
+      mlp_pe_bwd_kernel<<<(unsigned)gb, 256, 0, stream>>>(e);
+      D3G_LAUNCH_CHECK(0, stream); }
+    }
+    if (rows_timenet) {
+      MlpTimenetRowsArgs r;
+      r.dpe = ws.dpe; r.t = t; r.t_stride = t_stride; r.rows = n; r.thidden = ws.thidden;
+      r.tn0_w = p->timenet0_w; r.tn2_w = p->timenet2_w;
+      r.g_tn0_w = g->timenet0_w; r.g_tn0_b = g->timenet0_b; r.g_tn2_w = g->timenet2_w; r.g_tn2_b = g->timenet2_b;
+      r.dL_dt_rows = dL_dt; r.nonuniform = nonuniform;
+      int64_t gb = (n + 31) / 32;
+      if (gb > 2 * (int64_t)num_sms()) gb = 2 * (int64_t)num_sms();
+      { ProfScope _p(PROF_MLP_DPE, stream);
+      mlp_timenet_rows_kernel<<<(unsigned)gb, 256, 0, stream>>>(r);
+      D3G_LAUNCH_CHECK(0, stream); }
+    }
+  }
   return 0;
+}
+
+extern "C" int d3g_mlp_backward(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp_params* p,
+                                int64_t rows, const float* xyz, const float* t, int64_t t_stride, void* workspace,
+                                const float* dL_dxyz_out, const float* dL_drot, const float* dL_dscale,
+                                const d3g_mlp_grads* g, float* dL_dxyz, float* dL_dt, void* stream_) {
+  return mlp_backward_impl(cfg, packed, p, rows, 1, xyz, t, t_stride, workspace, dL_dxyz_out, dL_drot, dL_dscale, g,
+                           dL_dxyz, dL_dt, (cudaStream_t)stream_);
+}
+
+extern "C" int d3g_mlp_backward_times(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp_params* p,
+                                      int64_t n_points, int32_t n_times, const float* xyz, const float* t_values,
+                                      void* workspace, const float* dL_dxyz_out, const float* dL_drot,
+                                      const float* dL_dscale, const d3g_mlp_grads* g, float* dL_dxyz, float* dL_dt,
+                                      void* stream_) {
+  if (n_times < 1) return set_err(D3G_ERR_INVALID, "n_times must be >= 1");
+  return mlp_backward_impl(cfg, packed, p, n_points, n_times, xyz, t_values, 0, workspace, dL_dxyz_out, dL_drot,
+                           dL_dscale, g, dL_dxyz, dL_dt, (cudaStream_t)stream_);
 }
 
 // Parity / debug access: activation pattern of trunk layer `layer` as saved by a forward with

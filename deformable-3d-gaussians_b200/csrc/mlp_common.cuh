@@ -46,7 +46,7 @@ __host__ __device__ inline void bwd_stage_info(int st, int& layer, int& kpanel) 
 // Saved tiles are "MN-major wgrad images" (umma.cuh, layout (2)): exactly what the weight-gradient
 // kernel feeds to the tensor core as operands with K = points, so backward never re-arranges them.
 struct MlpWs {
-  int32_t* status;     // [0] abort flag
+  int32_t* status;     // [0] abort flag, [1] "rows carry different time values" (set on the device by forward)
   float* tfeat;        // [rows_t, 32]   time feature fed into pe columns 63..
   float* thidden;      // [rows_t, 256]  timenet hidden (post-ReLU), blender only
   uint8_t* pe_img;     // [tiles] x 48 KB            pe block (96 columns)
@@ -55,21 +55,40 @@ struct MlpWs {
   float* heads_out;    // [tiles*128, 16] head pre-outputs (incl. bias)
   uint8_t* dz_img;     // [8][tiles] x 128 KB        dL/d(pre-activation) tiles, written by backward
   uint8_t* dout_img;   // [tiles] x 16 KB            head cotangents (32 columns, 16 used)
-  float* scratch;      // kScratchFloats: head-bias sums [16] | fresh bias grads of layer 0 / 5 [2][256]
+  float* scratch;      // head-bias sums [16] | per time block: fresh bias grads of layer 0 / 5 [blocks][2][256]
+  float* dpe;          // [tiles*128, 96] dL/d(pe block) per row (general backward only)
+  size_t scratch_floats;
   size_t total;
 };
 
-constexpr int kScratchFloats = 16 + 512 + 48;
 constexpr uint32_t kDoutBytes = 4 * 4096;
 
-inline MlpWs mlp_ws_view(void* base, int64_t rows, bool save) {
+// A launch covers `blocks` time blocks of `rows` points each (blocks = 1: the plain [rows] call).  Every block
+// starts on a tile boundary, so a tile never mixes two time values.
+struct MlpShape {
+  int64_t n;            // points per block
+  int blocks;           // time values
+  int tpb;              // tiles per block
+  int tiles;            // blocks * tpb
+};
+inline MlpShape mlp_shape(int64_t n, int blocks) {
+  MlpShape s;
+  s.n = n; s.blocks = blocks < 1 ? 1 : blocks;
+  s.tpb = (int)((n + kRows - 1) / kRows);
+  if (s.tpb < 1) s.tpb = 1;
+  s.tiles = s.tpb * s.blocks;
+  return s;
+}
+
+inline MlpWs mlp_ws_view(void* base, int64_t rows, bool save, int blocks = 1) {
   MlpWs w;
   char* p = (char*)base;
   size_t off = 0;
   auto take = [&](size_t bytes) { char* r = p + off; off += align_up(bytes, 1024); return r; };
-  size_t tiles = (size_t)((rows + kRows - 1) / kRows);
-  if (tiles == 0) tiles = 1;
-  size_t r = (size_t)(rows > 0 ? rows : 1);
+  const MlpShape sh = mlp_shape(rows, blocks);
+  size_t tiles = (size_t)sh.tiles;
+  // time features: one row per point (plain call, rows may carry their own t) or one per time block
+  size_t r = blocks > 1 ? (size_t)blocks : (size_t)(rows > 0 ? rows : 1);
   w.status = (int32_t*)take(1024);
   w.tfeat = (float*)take(r * 32 * 4);
   w.thidden = (float*)take(save ? r * 256 * 4 : 1024);
@@ -80,10 +99,13 @@ inline MlpWs mlp_ws_view(void* base, int64_t rows, bool save) {
     w.heads_out = (float*)take(tiles * 128 * 16 * 4);
     w.dz_img = (uint8_t*)take(8 * tiles * (size_t)kHBytes);
     w.dout_img = (uint8_t*)take(tiles * (size_t)kDoutBytes);
-    w.scratch = (float*)take(kScratchFloats * 4);
+    w.scratch_floats = 16 + (size_t)sh.blocks * 512 + 48;
+    w.scratch = (float*)take(w.scratch_floats * 4);
+    w.dpe = (float*)take(tiles * 128 * 96 * 4);
   } else {
     w.pe_img = w.h_img = w.dz_img = w.dout_img = nullptr;
-    w.mask = nullptr; w.heads_out = nullptr; w.scratch = nullptr;
+    w.mask = nullptr; w.heads_out = nullptr; w.scratch = nullptr; w.dpe = nullptr;
+    w.scratch_floats = 0;
   }
   w.total = off;
   return w;

@@ -42,10 +42,12 @@ struct MlpFwdArgs {
   const uint8_t* wfwd;
   const float* bias;
   const float* xyz;
-  int64_t rows;
-  int tiles;
+  int64_t rows;          // points per time block
+  int tiles;             // all tiles of the launch (blocks * tpb)
+  int tpb;               // tiles per time block
   const float* tfeat;
-  int64_t tfeat_stride;  // 0 (uniform t) or 32
+  int per_row_t;         // rows carry their own time value (plain call with t_stride != 0): the stride is 32 unless
+  const int* nonuniform; // ... the device found all values equal (*nonuniform == 0), then row 0 serves every row
   int pe_dim, t_dim;
   int is_6dof, heads;
   int save;
@@ -198,15 +200,18 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
     const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
     uint32_t acc_ph = 0;
     bool ok = true;
+    const int64_t tfeat_stride = (a.per_row_t && *a.nonuniform) ? 32 : 0;
     for (int tile = blockIdx.x; ok && tile < a.tiles; tile += gridDim.x) {
-      const int64_t grow = (int64_t)tile * kRows + row;
-      const bool live = grow < a.rows;
+      const int blk = tile / a.tpb;
+      const int64_t prow = (int64_t)(tile - blk * a.tpb) * kRows + row;   // point index inside the time block
+      const bool live = prow < a.rows;
+      const int64_t grow = (int64_t)blk * a.rows + prow;                  // row of the [blocks, rows, .] outputs
       // ---- positional encoding block: each row is built by two threads (columns 0..47 / 48..95) in
       // registers, then written to shared memory (K-major SW128 image, A operand of layer 0 and of the
       // skip layer) and, when saving for backward, to HBM as an MN-major wgrad image ----
       if (cg < 2) {
         float x[3] = {0.f, 0.f, 0.f};
-        if (live) { x[0] = a.xyz[3 * grow]; x[1] = a.xyz[3 * grow + 1]; x[2] = a.xyz[3 * grow + 2]; }
+        if (live) { x[0] = a.xyz[3 * prow]; x[1] = a.xyz[3 * prow + 1]; x[2] = a.xyz[3 * prow + 2]; }
         float pe[48];
         if (chalf == 0) {
           pe[0] = x[0]; pe[1] = x[1]; pe[2] = x[2];
@@ -233,7 +238,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
               pe[6 * (f - 8) + 6 + d] = cs;
             }
           }
-          const float* tf = a.tfeat + (live ? grow * a.tfeat_stride : 0);
+          const float* tf = a.tfeat + (size_t)blk * 32 + (live ? prow * tfeat_stride : 0);
 #pragma unroll
           for (int j = 0; j < 33; j++) pe[15 + j] = (live && j < a.t_dim) ? tf[j] : 0.f;
         }
@@ -401,52 +406,69 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
 // small helper kernels
 // ------------------------------------------------------------------------------------------------
 
+// Do the rows of a per-row time tensor carry different values?  (train_baseline.py:110-115 materialises
+// `fid.expand(N,1) + ast_noise`, which for blender scenes is N copies of one value.)  flag[0] is zeroed by the
+// caller and set to 1 when any element differs from t[0]; the kernels downstream branch on it, so the shared-t
+// fast path needs no host round-trip.
+__global__ void __launch_bounds__(256)
+t_nonuniform_kernel(int64_t rows, const float* __restrict__ t, int64_t t_stride, int* __restrict__ flag) {
+  const float t0 = t[0];
+  int differs = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < rows; i += (int64_t)gridDim.x * blockDim.x)
+    differs |= (t[i * t_stride] != t0);
+  if (__syncthreads_or(differs) && threadIdx.x == 0) *flag = 1;
+}
+
 // Time feature: blender -> timenet(PE_6(t)) = 13 -> 256 -> ReLU -> 30 (utils/time_utils.py:74-76,105);
-// otherwise PE_10(t) (21 values).  One CTA of 256 threads per distinct time value.
+// otherwise PE_10(t) (21 values).  One CTA of 256 threads per distinct time value (grid-stride).  With
+// `nonuniform` given and clear, only row 0 is evaluated.
 __global__ void __launch_bounds__(256)
 tfeat_kernel(int64_t rows_t, const float* __restrict__ t, int64_t t_stride, int is_blender,
              const float* __restrict__ w0, const float* __restrict__ b0, const float* __restrict__ w2,
-             const float* __restrict__ b2, float* __restrict__ tfeat, float* __restrict__ thidden) {
+             const float* __restrict__ b2, float* __restrict__ tfeat, float* __restrict__ thidden,
+             const int* __restrict__ nonuniform) {
   __shared__ float e[32];
   __shared__ float hid[256];
-  int64_t r = blockIdx.x;
-  if (r >= rows_t) return;
-  float tv = t[r * t_stride];
-  int L = is_blender ? 6 : 10;
-  if (threadIdx.x < 32) {
-    int j = threadIdx.x;
-    float v = 0.f;
-    if (j == 0) v = tv;
-    else if (j < 1 + 2 * L) {
-      int f = (j - 1) >> 1;
-      float arg = tv * (float)(1 << f);
-      v = ((j - 1) & 1) ? cosf(arg) : sinf(arg);
+  if (nonuniform && !*nonuniform) rows_t = 1;
+  for (int64_t r = blockIdx.x; r < rows_t; r += gridDim.x) {
+    __syncthreads();
+    float tv = t[r * t_stride];
+    int L = is_blender ? 6 : 10;
+    if (threadIdx.x < 32) {
+      int j = threadIdx.x;
+      float v = 0.f;
+      if (j == 0) v = tv;
+      else if (j < 1 + 2 * L) {
+        int f = (j - 1) >> 1;
+        float arg = tv * (float)(1 << f);
+        v = ((j - 1) & 1) ? cosf(arg) : sinf(arg);
+      }
+      e[j] = v;
     }
-    e[j] = v;
-  }
-  __syncthreads();
-  if (!is_blender) {
-    if (threadIdx.x < 32) tfeat[r * 32 + threadIdx.x] = threadIdx.x < 21 ? e[threadIdx.x] : 0.f;
-    return;
-  }
-  {
-    int j = threadIdx.x;
-    float acc = b0[j];
+    __syncthreads();
+    if (!is_blender) {
+      if (threadIdx.x < 32) tfeat[r * 32 + threadIdx.x] = threadIdx.x < 21 ? e[threadIdx.x] : 0.f;
+      continue;
+    }
+    {
+      int j = threadIdx.x;
+      float acc = b0[j];
 #pragma unroll
-    for (int k = 0; k < 13; k++) acc += w0[j * 13 + k] * e[k];
-    acc = fmaxf(acc, 0.f);
-    hid[j] = acc;
-    if (thidden) thidden[r * 256 + j] = acc;
-  }
-  __syncthreads();
-  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int i = warp; i < 32; i += 8) {
-    float acc = 0.f;
-    if (i < 30)
-      for (int k = lane; k < 256; k += 32) acc += w2[i * 256 + k] * hid[k];
+      for (int k = 0; k < 13; k++) acc += w0[j * 13 + k] * e[k];
+      acc = fmaxf(acc, 0.f);
+      hid[j] = acc;
+      if (thidden) thidden[r * 256 + j] = acc;
+    }
+    __syncthreads();
+    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = warp; i < 32; i += 8) {
+      float acc = 0.f;
+      if (i < 30)
+        for (int k = lane; k < 256; k += 32) acc += w2[i * 256 + k] * hid[k];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if (lane == 0) tfeat[r * 32 + i] = i < 30 ? acc + b2[i] : 0.f;
+      for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if (lane == 0) tfeat[r * 32 + i] = i < 30 ? acc + b2[i] : 0.f;
+    }
   }
 }
 
@@ -553,15 +575,16 @@ int check_cfg(const d3g_mlp_config* cfg) {
   return 0;
 }
 
-static int g_num_sms = 0;
+static int g_num_sms[64] = {};   // per device
 int num_sms() {
-  if (!g_num_sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-    if (g_num_sms <= 0) g_num_sms = 148;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) return 148;
+  if (!g_num_sms[dev]) {
+    cudaDeviceGetAttribute(&g_num_sms[dev], cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms[dev] <= 0) g_num_sms[dev] = 148;
   }
-  return g_num_sms;
+  return g_num_sms[dev];
 }
 
 }  // namespace d3g
@@ -584,6 +607,14 @@ int d3g_mlp_workspace_bytes(const d3g_mlp_config* cfg, int64_t rows, int32_t sav
   return 0;
 }
 
+int d3g_mlp_workspace_bytes_times(const d3g_mlp_config* cfg, int64_t n_points, int32_t n_times, int32_t save,
+                                  size_t* bytes) {
+  if (int e = check_cfg(cfg)) return e;
+  if (!bytes || n_points < 0 || n_times < 1) return set_err(D3G_ERR_INVALID, "bad arguments");
+  *bytes = mlp_ws_view(nullptr, n_points, save != 0, n_times).total;
+  return 0;
+}
+
 int d3g_mlp_pack_weights(const d3g_mlp_config* cfg, const d3g_mlp_params* p, void* packed, void* stream_) {
   if (int e = check_cfg(cfg)) return e;
   if (!p || !packed) return set_err(D3G_ERR_INVALID, "NULL argument");
@@ -599,30 +630,43 @@ int d3g_mlp_pack_weights(const d3g_mlp_config* cfg, const d3g_mlp_params* p, voi
   return 0;
 }
 
-int d3g_mlp_forward(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp_params* p, int64_t rows,
-                    const float* xyz, const float* t, int64_t t_stride, void* workspace, int32_t save,
-                    float* d_xyz, float* d_rot, float* d_scale, void* stream_) {
+// One implementation behind both entry points: `blocks` time blocks of `n` points each (plain call: blocks = 1
+// and t / t_stride describe per-row values; times call: t holds one value per block).
+static int mlp_forward_impl(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp_params* p, int64_t n,
+                            int blocks, const float* xyz, const float* t, int64_t t_stride, void* workspace,
+                            int32_t save, float* d_xyz, float* d_rot, float* d_scale, cudaStream_t stream) {
   if (int e = check_cfg(cfg)) return e;
   if (!packed || !p || !workspace) return set_err(D3G_ERR_INVALID, "NULL argument");
-  if (rows < 0 || (rows > 0 && (!xyz || !t || !d_xyz))) return set_err(D3G_ERR_INVALID, "NULL tensor");
+  if (n < 0 || blocks < 1 || (n > 0 && (!xyz || !t || !d_xyz))) return set_err(D3G_ERR_INVALID, "NULL tensor");
   if (cfg->is_blender && (!p->timenet0_w || !p->timenet0_b || !p->timenet2_w || !p->timenet2_b))
     return set_err(D3G_ERR_INVALID, "timenet parameters missing");
-  if (rows > ((int64_t)1 << 31) - 256) return set_err(D3G_ERR_CAPACITY, "too many rows");
-  cudaStream_t stream = (cudaStream_t)stream_;
-  MlpWs ws = mlp_ws_view(workspace, rows, save != 0);
-  D3G_CUDA_TRY(cudaMemsetAsync(ws.status, 0, 4, stream));
-  if (rows == 0) return 0;
-  int64_t rows_t = t_stride == 0 ? 1 : rows;
+  const MlpShape sh = mlp_shape(n, blocks);
+  if ((int64_t)sh.tpb * blocks > ((int64_t)1 << 24)) return set_err(D3G_ERR_CAPACITY, "too many rows");
+  MlpWs ws = mlp_ws_view(workspace, n, save != 0, blocks);
+  D3G_CUDA_TRY(cudaMemsetAsync(ws.status, 0, 8, stream));
+  if (n == 0) return 0;
+  const bool per_row = blocks == 1 && t_stride != 0 && n > 1;
+  const int64_t rows_t = per_row ? n : blocks;
+  const int64_t tstride_eff = per_row ? t_stride : (blocks > 1 ? 1 : 0);
+  int* nonuniform = ws.status + 1;
+  if (per_row) {
+    int g = (int)((n + 255) / 256);
+    if (g > 4 * num_sms()) g = 4 * num_sms();
+    ProfScope _p(PROF_MLP_TFEAT, stream);
+    t_nonuniform_kernel<<<g, 256, 0, stream>>>(n, t, t_stride, nonuniform);
+    D3G_LAUNCH_CHECK(0, stream);
+  }
   { ProfScope _p(PROF_MLP_TFEAT, stream);
-    tfeat_kernel<<<(unsigned)rows_t, 256, 0, stream>>>(rows_t, t, t_stride, cfg->is_blender, p->timenet0_w,
-                                                     p->timenet0_b, p->timenet2_w, p->timenet2_b, ws.tfeat,
-                                                     save ? ws.thidden : nullptr);
+    int64_t g = rows_t < 8 * (int64_t)num_sms() ? rows_t : 8 * (int64_t)num_sms();
+    tfeat_kernel<<<(unsigned)g, 256, 0, stream>>>(rows_t, t, tstride_eff, cfg->is_blender, p->timenet0_w,
+                                                  p->timenet0_b, p->timenet2_w, p->timenet2_b, ws.tfeat,
+                                                  save ? ws.thidden : nullptr, per_row ? nonuniform : nullptr);
   D3G_LAUNCH_CHECK(0, stream); }
   MlpFwdArgs a;
   a.wfwd = (const uint8_t*)packed;
   a.bias = (const float*)((const uint8_t*)packed + kBiasOff);
-  a.xyz = xyz; a.rows = rows; a.tiles = (int)((rows + kRows - 1) / kRows);
-  a.tfeat = ws.tfeat; a.tfeat_stride = t_stride == 0 ? 0 : 32;
+  a.xyz = xyz; a.rows = n; a.tiles = sh.tiles; a.tpb = sh.tpb;
+  a.tfeat = ws.tfeat; a.per_row_t = per_row ? 1 : 0; a.nonuniform = nonuniform;
   a.pe_dim = cfg->is_blender ? 93 : 84; a.t_dim = cfg->is_blender ? 30 : 21;
   a.is_6dof = cfg->is_6dof; a.heads = cfg->heads; a.save = save != 0;
   a.pe_img = ws.pe_img; a.h_img = ws.h_img; a.mask = ws.mask; a.heads_out = ws.heads_out;
@@ -635,6 +679,21 @@ int d3g_mlp_forward(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp
     mlp_fwd_kernel<<<grid, kFwdThreads, smem, stream>>>(a);
   D3G_LAUNCH_CHECK(0, stream); }
   return 0;
+}
+
+int d3g_mlp_forward(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp_params* p, int64_t rows,
+                    const float* xyz, const float* t, int64_t t_stride, void* workspace, int32_t save,
+                    float* d_xyz, float* d_rot, float* d_scale, void* stream_) {
+  return mlp_forward_impl(cfg, packed, p, rows, 1, xyz, t, t_stride, workspace, save, d_xyz, d_rot, d_scale,
+                          (cudaStream_t)stream_);
+}
+
+int d3g_mlp_forward_times(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp_params* p, int64_t n_points,
+                          int32_t n_times, const float* xyz, const float* t_values, void* workspace, int32_t save,
+                          float* d_xyz, float* d_rot, float* d_scale, void* stream_) {
+  if (n_times < 1) return set_err(D3G_ERR_INVALID, "n_times must be >= 1");
+  return mlp_forward_impl(cfg, packed, p, n_points, n_times, xyz, t_values, 0, workspace, save, d_xyz, d_rot,
+                          d_scale, (cudaStream_t)stream_);
 }
 
 int d3g_mlp_read_status(const void* workspace, int32_t* status_host, void* stream_) {

@@ -53,8 +53,11 @@ def _fill_ptr_struct(struct, named):
 
 
 class _FusedDeform(torch.autograd.Function):
+    """One fused launch.  mode "times": t holds T time values, each applied to all N points (outputs [T,N,.]);
+    mode "rows": t holds one value per row (any non-zero stride; outputs [N,.])."""
+
     @staticmethod
-    def forward(ctx, net, need_grad, xyz, t, *params):
+    def forward(ctx, net, need_grad, mode, xyz, t, *params):
         lib = _lib.load()
         dev = xyz.device
         if dev.type != "cuda":
@@ -62,32 +65,43 @@ class _FusedDeform(torch.autograd.Function):
         xyz_c = xyz.detach().contiguous().float()
         rows = int(xyz_c.shape[0])
         t2 = t.detach()
-        if t2.dim() == 2:
-            t2 = t2[:, 0]
         if t2.dtype != torch.float32:
             t2 = t2.float()
-        if t2.numel() == 1:
-            t_stride = 0
-        else:
-            t_stride = int(t2.stride(0))
         cfg = net._cfg()
-        packed = net._packed(dev)
         wsb = C.c_size_t()
-        _lib.check(lib.d3g_mlp_workspace_bytes(C.byref(cfg), rows, int(need_grad), C.byref(wsb)))
-        ws = torch.empty(wsb.value, dtype=torch.uint8, device=dev)
-        pstruct = _fill_ptr_struct(_lib.MlpParams(), _param_list(net))
-        d_xyz = torch.empty((rows, 4, 4) if net.is_6dof else (rows, 3), dtype=torch.float32, device=dev)
-        d_rot = torch.empty(rows, 4, dtype=torch.float32, device=dev) if net._heads & HEAD_ROT else None
-        d_scale = torch.empty(rows, 3, dtype=torch.float32, device=dev) if net._heads & HEAD_SCALE else None
-        stream = torch.cuda.current_stream().cuda_stream
-        _lib.check(lib.d3g_mlp_forward(C.byref(cfg), _lib.ptr(packed), C.byref(pstruct), C.c_int64(rows),
-                                       _lib.ptr(xyz_c), _lib.ptr(t2), C.c_int64(t_stride), _lib.ptr(ws),
-                                       int(need_grad), _lib.ptr(d_xyz), _lib.ptr(d_rot), _lib.ptr(d_scale),
-                                       C.c_void_p(stream)))
-        if net.debug:
-            net._check_status(ws)
-        ctx.net, ctx.ws, ctx.rows, ctx.t_stride = net, ws, rows, t_stride
+        with torch.cuda.device(dev):
+            packed = net._packed(dev)
+            stream = torch.cuda.current_stream().cuda_stream
+            pstruct = _fill_ptr_struct(_lib.MlpParams(), _param_list(net))
+            if mode == "times":
+                t2 = t2.reshape(-1).contiguous()
+                T = int(t2.numel())
+                lead = (T, rows)
+                _lib.check(lib.d3g_mlp_workspace_bytes_times(C.byref(cfg), rows, T, int(need_grad), C.byref(wsb)))
+            else:
+                T = 0
+                lead = (rows,)
+                if t2.dim() != 1 or t2.shape[0] != rows:
+                    raise RuntimeError("DeformNetwork: per-row time tensor must have one value per point")
+                _lib.check(lib.d3g_mlp_workspace_bytes(C.byref(cfg), rows, int(need_grad), C.byref(wsb)))
+            ws = torch.empty(wsb.value, dtype=torch.uint8, device=dev)
+            d_xyz = torch.empty(lead + ((4, 4) if net.is_6dof else (3,)), dtype=torch.float32, device=dev)
+            d_rot = torch.empty(lead + (4,), dtype=torch.float32, device=dev) if net._heads & HEAD_ROT else None
+            d_scale = torch.empty(lead + (3,), dtype=torch.float32, device=dev) if net._heads & HEAD_SCALE else None
+            if mode == "times":
+                _lib.check(lib.d3g_mlp_forward_times(C.byref(cfg), _lib.ptr(packed), C.byref(pstruct),
+                                                     C.c_int64(rows), T, _lib.ptr(xyz_c), _lib.ptr(t2), _lib.ptr(ws),
+                                                     int(need_grad), _lib.ptr(d_xyz), _lib.ptr(d_rot),
+                                                     _lib.ptr(d_scale), C.c_void_p(stream)))
+            else:
+                _lib.check(lib.d3g_mlp_forward(C.byref(cfg), _lib.ptr(packed), C.byref(pstruct), C.c_int64(rows),
+                                               _lib.ptr(xyz_c), _lib.ptr(t2), C.c_int64(int(t2.stride(0))),
+                                               _lib.ptr(ws), int(need_grad), _lib.ptr(d_xyz), _lib.ptr(d_rot),
+                                               _lib.ptr(d_scale), C.c_void_p(stream)))
+            net._watch_status(ws)
+        ctx.net, ctx.ws, ctx.rows, ctx.mode, ctx.T = net, ws, rows, mode, T
         ctx.xyz_requires_grad = xyz.requires_grad
+        ctx.t_requires_grad = t.requires_grad
         ctx.save_for_backward(xyz_c, t2)
         ctx.set_materialize_grads(False)
         outs = [d_xyz]
@@ -104,6 +118,9 @@ class _FusedDeform(torch.autograd.Function):
         xyz_c, t2 = ctx.saved_tensors
         dev = xyz_c.device
         rows = ctx.rows
+        if ctx.ws is None:
+            raise RuntimeError("DeformNetwork: backward through the same forward twice (the saved activations are "
+                               "released after the first backward, as with retain_graph=False)")
         it = iter(gouts)
         g_xyz = next(it)
         g_rot = next(it) if net._heads & HEAD_ROT else None
@@ -118,35 +135,46 @@ class _FusedDeform(torch.autograd.Function):
         direct = net.fused_grad_accumulation and all(
             p.grad is not None and p.grad.dtype == torch.float32 and p.grad.is_contiguous() and p.grad.device == dev
             for _, p in named if p.requires_grad)
-        if direct:
-            scratch = None
-            grads = []
-            for _, p in named:
-                if p.requires_grad:
-                    grads.append(p.grad)
-                else:  # frozen parameter: its gradient goes to a scratch buffer nobody reads
-                    if scratch is None:
-                        scratch = torch.empty(max(q.numel() for _, q in named), dtype=torch.float32, device=dev)
-                    grads.append(scratch[:p.numel()].view_as(p))
-        else:
-            sizes = [(p.numel() + 3) // 4 * 4 for _, p in named]  # keep every view 16-byte aligned
-            flat = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
-            grads, off = [], 0
-            for (_, p), n in zip(named, sizes):
-                grads.append(flat[off:off + p.numel()].view_as(p))
-                off += n
-        gstruct = _fill_ptr_struct(_lib.MlpGrads(), [(n, g) for (n, _), g in zip(named, grads)])
-        pstruct = _fill_ptr_struct(_lib.MlpParams(), named)
-        cfg = net._cfg()
-        packed = net._packed(dev)
-        dxyz_in = torch.empty(rows, 3, dtype=torch.float32, device=dev) if ctx.xyz_requires_grad else None
-        stream = torch.cuda.current_stream().cuda_stream
-        _lib.check(lib.d3g_mlp_backward(C.byref(cfg), _lib.ptr(packed), C.byref(pstruct), C.c_int64(rows),
-                                        _lib.ptr(xyz_c), _lib.ptr(t2), C.c_int64(ctx.t_stride), _lib.ptr(ctx.ws),
-                                        _lib.ptr(g_xyz), _lib.ptr(g_rot), _lib.ptr(g_scale), C.byref(gstruct),
-                                        _lib.ptr(dxyz_in), C.c_void_p(0), C.c_void_p(stream)))
-        if net.debug:
-            net._check_status(ctx.ws)
+        with torch.cuda.device(dev):
+            if direct:
+                scratch = None
+                grads = []
+                for _, p in named:
+                    if p.requires_grad:
+                        grads.append(p.grad)
+                    else:  # frozen parameter: its gradient goes to a scratch buffer nobody reads
+                        if scratch is None:
+                            scratch = torch.empty(max(q.numel() for _, q in named), dtype=torch.float32, device=dev)
+                        grads.append(scratch[:p.numel()].view_as(p))
+            else:
+                sizes = [(p.numel() + 3) // 4 * 4 for _, p in named]  # keep every view 16-byte aligned
+                flat = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
+                grads, off = [], 0
+                for (_, p), n in zip(named, sizes):
+                    grads.append(flat[off:off + p.numel()].view_as(p))
+                    off += n
+            gstruct = _fill_ptr_struct(_lib.MlpGrads(), [(n, g) for (n, _), g in zip(named, grads)])
+            pstruct = _fill_ptr_struct(_lib.MlpParams(), named)
+            cfg = net._cfg()
+            packed = net._packed(dev)
+            dxyz_in = torch.empty(rows, 3, dtype=torch.float32, device=dev) if ctx.xyz_requires_grad else None
+            dt_in = None
+            if ctx.t_requires_grad:
+                dt_in = torch.empty(ctx.T if ctx.mode == "times" else rows, dtype=torch.float32, device=dev)
+            stream = torch.cuda.current_stream().cuda_stream
+            if ctx.mode == "times":
+                _lib.check(lib.d3g_mlp_backward_times(C.byref(cfg), _lib.ptr(packed), C.byref(pstruct),
+                                                      C.c_int64(rows), ctx.T, _lib.ptr(xyz_c), _lib.ptr(t2),
+                                                      _lib.ptr(ctx.ws), _lib.ptr(g_xyz), _lib.ptr(g_rot),
+                                                      _lib.ptr(g_scale), C.byref(gstruct), _lib.ptr(dxyz_in),
+                                                      _lib.ptr(dt_in), C.c_void_p(stream)))
+            else:
+                _lib.check(lib.d3g_mlp_backward(C.byref(cfg), _lib.ptr(packed), C.byref(pstruct), C.c_int64(rows),
+                                                _lib.ptr(xyz_c), _lib.ptr(t2), C.c_int64(int(t2.stride(0))),
+                                                _lib.ptr(ctx.ws), _lib.ptr(g_xyz), _lib.ptr(g_rot),
+                                                _lib.ptr(g_scale), C.byref(gstruct), _lib.ptr(dxyz_in),
+                                                _lib.ptr(dt_in), C.c_void_p(stream)))
+            net._watch_status(ctx.ws)
         _FusedDeform.last_ws = ctx.ws if net.debug else None  # parity inspection hook (tools/dbg_mlp_bwd.py)
         ctx.ws = None
         # heads the network never evaluates get no gradient at all (like autograd in the reference), so
@@ -160,7 +188,7 @@ class _FusedDeform(torch.autograd.Function):
             out = tuple(None for _ in named)
         else:
             out = tuple(None if n in unused else g for (n, _), g in zip(named, grads))
-        return (None, None, dxyz_in, None) + out
+        return (None, None, None, dxyz_in, dt_in) + out
 
 
 class _DeformBase(nn.Module):
@@ -200,6 +228,7 @@ class _DeformBase(nn.Module):
         # with loss.backward()-style accumulation, not with torch.autograd.grad()
         self.fused_grad_accumulation = False
         self._pack_cache = None
+        self._status_pending, self._status_host, self._status_next = [], None, 0
 
     # -- C-ABI plumbing --------------------------------------------------------------------------
     def _cfg(self):
@@ -229,13 +258,41 @@ class _DeformBase(nn.Module):
         self._pack_cache = (key, buf)
         return buf
 
-    def _check_status(self, ws):
-        lib = _lib.load()
-        st = C.c_int32(0)
-        _lib.check(lib.d3g_mlp_read_status(_lib.ptr(ws), C.byref(st),
-                                           C.c_void_p(torch.cuda.current_stream().cuda_stream)))
-        if st.value != 0:
-            raise _lib.D3GError("fused MLP kernel reported an internal pipeline timeout (status %d)" % st.value)
+    def _watch_status(self, ws):
+        """The kernels' bounded mbarrier waits set a status word instead of hanging.  It is copied to pinned host
+        memory on the stream right behind the launch and examined once that copy has completed — at the next
+        call, or in check_status() — so a pipeline abort never goes unnoticed and the hot path never syncs.
+        With debug set (D3G_DEBUG=1) the check is immediate."""
+        self._poll_status(wait=len(self._status_pending) >= 32)
+        if self._status_host is None:
+            self._status_host = torch.zeros(64, dtype=torch.int32).pin_memory()
+        i = self._status_next
+        self._status_next = (i + 1) % 64
+        slot = self._status_host[i:i + 1]
+        slot.copy_(ws[:4].view(torch.int32), non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self._status_pending.append((ev, slot))
+        if self.debug:
+            self.check_status()
+
+    def _poll_status(self, wait=False):
+        keep = []
+        for ev, slot in self._status_pending:
+            if wait:
+                ev.synchronize()
+            if wait or ev.query():
+                if int(slot[0]) != 0:
+                    self._status_pending = []
+                    raise _lib.D3GError("fused MLP kernel reported an internal pipeline timeout (status %d); its "
+                                        "outputs are invalid" % int(slot[0]))
+            else:
+                keep.append((ev, slot))
+        self._status_pending = keep
+
+    def check_status(self):
+        """Wait for every launch issued so far and raise if one of them aborted."""
+        self._poll_status(wait=True)
 
     def read_activation_masks(self, ws, rows):
         """Parity hook: [8, rows, 256] bool activation pattern saved by the last training-mode forward."""
@@ -252,10 +309,38 @@ class _DeformBase(nn.Module):
         return out
 
     def _run(self, x, t):
+        """forward(x, t) of the reference: t is [N,1] (utils/time_utils.py:102-103).  One value shared by every
+        row (the `fid.expand(N,1)` of train.py:207, or a single element) goes down the time-block path with
+        T = 1; anything else is a per-row launch, whatever its stride."""
         params = [p for _, p in _param_list(self)]
         # (grad mode is off inside autograd.Function.forward, so decide here whether to save activations)
-        need_grad = torch.is_grad_enabled() and (any(p.requires_grad for p in params) or x.requires_grad)
-        return _FusedDeform.apply(self, need_grad, x, t, *params)
+        need_grad = torch.is_grad_enabled() and (any(p.requires_grad for p in params) or x.requires_grad
+                                                 or t.requires_grad)
+        N = x.shape[0]
+        if t.dim() == 2:
+            if t.shape[1] != 1:
+                raise RuntimeError("DeformNetwork.forward expects t of shape [N,1] (got %s)" % (tuple(t.shape),))
+            shared = t.shape[0] == 1 or (t.shape[0] == N and t.stride(0) == 0)
+            tv = t[:1].reshape(1) if shared else t[:, 0]
+        elif t.dim() <= 1:
+            shared = t.numel() == 1 or (t.numel() == N and t.stride(0) == 0)
+            tv = t.reshape(-1)[:1] if shared else t
+        else:
+            raise RuntimeError("DeformNetwork.forward expects t of shape [N,1]")
+        if not shared and tv.shape[0] != N:
+            raise RuntimeError("DeformNetwork.forward: t has %d rows, x has %d" % (tv.shape[0], N))
+        if shared:
+            outs = _FusedDeform.apply(self, need_grad, "times", x, tv, *params)
+            return tuple(o[0] for o in outs)
+        return _FusedDeform.apply(self, need_grad, "rows", x, tv, *params)
+
+    def forward_times(self, x, t_values):
+        """T time values applied to the same N points in ONE launch: the loop of scene/deform_model.py:266-272
+        without its T launches.  Returns tensors shaped [T,N,.]."""
+        params = [p for _, p in _param_list(self)]
+        need_grad = torch.is_grad_enabled() and (any(p.requires_grad for p in params) or x.requires_grad
+                                                 or t_values.requires_grad)
+        return _FusedDeform.apply(self, need_grad, "times", x, t_values.reshape(-1), *params)
 
 
 class DeformNetworkBaseline(_DeformBase):
@@ -328,8 +413,13 @@ class DeformModel(_DeformModelBase):
         self.scale_lr = scale_lr
 
     def step(self, xyz, time_emb):
+        T = time_emb.shape[1]
+        if time_emb.shape[0] == 1 or time_emb.stride(0) == 0:
+            # every column is one time value (an expanded fid vector): all T timestamps in one launch
+            (d_xyz,) = self.deform.forward_times(xyz, time_emb[0])
+            return d_xyz, [0] * T, [0] * T
         d_xyz_list, d_rotation_list, d_scaling_list = [], [], []
-        for i in range(time_emb.shape[1]):
+        for i in range(T):
             d_xyz, d_rotation, d_scaling = self.deform(xyz, time_emb[:, i].unsqueeze(1))
             d_xyz_list.append(d_xyz)
             d_rotation_list.append(d_rotation)

@@ -29,9 +29,10 @@ class _ImageLoss(torch.autograd.Function):
         _lib.check(lib.d3g_image_loss_workspace_bytes(Cn, H, W, C.byref(nb)))
         ws = torch.empty(nb.value, dtype=torch.uint8, device=x.device)
         out = torch.empty(3, dtype=torch.float32, device=x.device)
-        _lib.check(lib.d3g_image_loss(Cn, H, W, _lib.ptr(x), _lib.ptr(y), C.c_float(w_l1), C.c_float(w_ssim),
-                                      C.c_float(bias), _lib.ptr(ws), _lib.ptr(out), None,
-                                      C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        with torch.cuda.device(x.device):
+            _lib.check(lib.d3g_image_loss(Cn, H, W, _lib.ptr(x), _lib.ptr(y), C.c_float(w_l1), C.c_float(w_ssim),
+                                          C.c_float(bias), _lib.ptr(ws), _lib.ptr(out), None,
+                                          C.c_void_p(torch.cuda.current_stream().cuda_stream)))
         ctx.saved = (x, y, ws, Cn, H, W, w_l1, w_ssim, img.shape)
         ctx.terms = out
         return out[2]
@@ -44,9 +45,10 @@ class _ImageLoss(torch.autograd.Function):
         x, y, ws, Cn, H, W, w_l1, w_ssim, shape = ctx.saved
         g = g.detach().reshape(1).float().contiguous()
         grad = torch.empty_like(x)
-        _lib.check(lib.d3g_image_loss_backward(Cn, H, W, _lib.ptr(x), _lib.ptr(y), C.c_float(w_l1), C.c_float(w_ssim),
-                                               _lib.ptr(ws), _lib.ptr(g), _lib.ptr(grad),
-                                               C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        with torch.cuda.device(x.device):
+            _lib.check(lib.d3g_image_loss_backward(Cn, H, W, _lib.ptr(x), _lib.ptr(y), C.c_float(w_l1),
+                                                   C.c_float(w_ssim), _lib.ptr(ws), _lib.ptr(g), _lib.ptr(grad),
+                                                   C.c_void_p(torch.cuda.current_stream().cuda_stream)))
         return grad.view(shape), None, None, None, None
 
 

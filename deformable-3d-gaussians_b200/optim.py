@@ -43,10 +43,14 @@ class Adam(torch.optim.Adam):
                 st["step"] += 1
                 t = _lib.AdamTensor(p.data_ptr(), g.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr(),
                                     p.numel(), float(group["lr"]), float(group["weight_decay"]), int(st["step"].item()))
-                by_cfg.setdefault((float(beta1), float(beta2), float(group["eps"]), p.device.index), []).append((t, g))
+                by_cfg.setdefault((float(beta1), float(beta2), float(group["eps"]), p.device.index), []).append((t, g, p))
         for (beta1, beta2, eps, dev), items in by_cfg.items():
-            arr = (_lib.AdamTensor * len(items))(*[t for t, _ in items])
+            arr = (_lib.AdamTensor * len(items))(*[t for t, _, _ in items])
             with torch.cuda.device(dev):
-                _lib.check(lib.d3g_adam_step(len(items), arr, C.c_float(beta1), C.c_float(beta2), C.c_float(eps),
+                _lib.check(lib.d3g_adam_step(len(items), arr, C.c_double(beta1), C.c_double(beta2), C.c_double(eps),
                                              C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+            # the kernel wrote through raw pointers: tell autograd (and every cache keyed on tensor versions,
+            # e.g. DeformNetwork's packed weight images) that the parameters changed
+            for _, _, p in items:
+                torch.autograd.graph.increment_version(p)
         return loss

@@ -149,51 +149,52 @@ class RasterState:
 
 def rasterize_forward(rs, means3D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp):
     """Forward through the C ABI. Returns (color, radii, depth, RasterState)."""
-    lib = _lib.load()
     dev = means3D.device
     if dev.type != "cuda":
         raise RuntimeError("GaussianRasterizer: tensors must live on a CUDA device (there is no CPU path)")
-    keep = []
-    s = _settings_struct(rs, keep)
-    N = int(means3D.shape[0])
-    H, W = s.image_height, s.image_width
-    M = int(shs.shape[1]) if shs is not None else 0
-    stream = torch.cuda.current_stream().cuda_stream
-    gb, ib = _sizes(lib, N, H, W)
-    geom = torch.empty(gb, dtype=torch.uint8, device=dev)
-    img = torch.empty(ib, dtype=torch.uint8, device=dev)
-    radii = torch.empty(N, dtype=torch.int32, device=dev)
-    color = torch.empty(3, H, W, dtype=torch.float32, device=dev)
-    depth = torch.empty(1, H, W, dtype=torch.float32, device=dev)
-    policy = PAIR_CAPACITY_POLICY
-    host = None if policy is not None else _pinned_u32(dev)
-    _lib.check(lib.d3g_raster_preprocess(C.byref(s), N, _lib.ptr(means3D), _lib.ptr(shs), M,
-                                         _lib.ptr(colors_precomp), _lib.ptr(opacities), _lib.ptr(scales),
-                                         _lib.ptr(rotations), _lib.ptr(cov3D_precomp), _lib.ptr(geom),
-                                         _lib.ptr(radii), C.c_void_p(0 if host is None else host.data_ptr()),
+    with torch.cuda.device(dev):
+        lib = _lib.load()
+        keep = []
+        s = _settings_struct(rs, keep)
+        N = int(means3D.shape[0])
+        H, W = s.image_height, s.image_width
+        M = int(shs.shape[1]) if shs is not None else 0
+        stream = torch.cuda.current_stream().cuda_stream
+        gb, ib = _sizes(lib, N, H, W)
+        geom = torch.empty(gb, dtype=torch.uint8, device=dev)
+        img = torch.empty(ib, dtype=torch.uint8, device=dev)
+        radii = torch.empty(N, dtype=torch.int32, device=dev)
+        color = torch.empty(3, H, W, dtype=torch.float32, device=dev)
+        depth = torch.empty(1, H, W, dtype=torch.float32, device=dev)
+        policy = PAIR_CAPACITY_POLICY
+        host = None if policy is not None else _pinned_u32(dev)
+        _lib.check(lib.d3g_raster_preprocess(C.byref(s), N, _lib.ptr(means3D), _lib.ptr(shs), M,
+                                             _lib.ptr(colors_precomp), _lib.ptr(opacities), _lib.ptr(scales),
+                                             _lib.ptr(rotations), _lib.ptr(cov3D_precomp), _lib.ptr(geom),
+                                             _lib.ptr(radii), C.c_void_p(0 if host is None else host.data_ptr()),
+                                             C.c_void_p(stream)))
+        cap = None if policy is None else policy(N, H, W)
+        if cap is None:
+            if host is None:
+                host = _pinned_u32(dev)
+                _lib.check(lib.d3g_raster_header_async(_lib.ptr(geom), C.c_void_p(host.data_ptr()), C.c_void_p(stream)))
+            torch.cuda.current_stream().synchronize()
+            R = int(host[0].item()) & 0xFFFFFFFF
+            cap = R
+            if hasattr(policy, "record_exact"):
+                policy.record_exact((N, H, W), R)
+        else:
+            R = None
+            cap = int(cap)
+        bb = C.c_size_t()
+        _lib.check(lib.d3g_raster_bin_bytes(C.c_uint64(cap), C.byref(bb)))
+        binb = torch.empty(bb.value, dtype=torch.uint8, device=dev)
+        _lib.check(lib.d3g_raster_render(C.byref(s), N, C.c_uint64(cap), _lib.ptr(geom), _lib.ptr(binb),
+                                         _lib.ptr(img), _lib.ptr(radii), _lib.ptr(color), _lib.ptr(depth),
                                          C.c_void_p(stream)))
-    cap = None if policy is None else policy(N, H, W)
-    if cap is None:
-        if host is None:
-            host = _pinned_u32(dev)
-            _lib.check(lib.d3g_raster_header_async(_lib.ptr(geom), C.c_void_p(host.data_ptr()), C.c_void_p(stream)))
-        torch.cuda.current_stream().synchronize()
-        R = int(host[0].item()) & 0xFFFFFFFF
-        cap = R
-        if hasattr(policy, "record_exact"):
-            policy.record_exact((N, H, W), R)
-    else:
-        R = None
-        cap = int(cap)
-    bb = C.c_size_t()
-    _lib.check(lib.d3g_raster_bin_bytes(C.c_uint64(cap), C.byref(bb)))
-    binb = torch.empty(bb.value, dtype=torch.uint8, device=dev)
-    _lib.check(lib.d3g_raster_render(C.byref(s), N, C.c_uint64(cap), _lib.ptr(geom), _lib.ptr(binb),
-                                     _lib.ptr(img), _lib.ptr(radii), _lib.ptr(color), _lib.ptr(depth),
-                                     C.c_void_p(stream)))
-    if R is None and hasattr(policy, "observe"):
-        policy.observe((N, H, W), cap, geom, lib)   # {R, overflow} of this frame, checked off the critical path
-    return color, radii, depth, RasterState(N, H, W, cap, geom, binb, img, R)
+        if R is None and hasattr(policy, "observe"):
+            policy.observe((N, H, W), cap, geom, lib)   # {R, overflow} of this frame, checked off the critical path
+        return color, radii, depth, RasterState(N, H, W, cap, geom, binb, img, R)
 
 
 class _RasterizeGaussians(torch.autograd.Function):
@@ -215,6 +216,11 @@ class _RasterizeGaussians(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, grad_color, _grad_radii, grad_depth):
+        with torch.cuda.device(ctx.saved_tensors[0].device):
+            return _RasterizeGaussians._backward(ctx, grad_color, _grad_radii, grad_depth)
+
+    @staticmethod
+    def _backward(ctx, grad_color, _grad_radii, grad_depth):
         lib = _lib.load()
         means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp, radii = ctx.saved_tensors
         st = ctx.state
@@ -255,7 +261,7 @@ class GaussianRasterizer(nn.Module):
 
     def markVisible(self, positions):
         lib = _lib.load()
-        with torch.no_grad():
+        with torch.no_grad(), torch.cuda.device(positions.device):
             positions = _f32c(positions)
             view = _f32c(self.raster_settings.viewmatrix)
             out = torch.empty(positions.shape[0], dtype=torch.uint8, device=positions.device)

@@ -24,6 +24,12 @@ class _PrepareGaussians(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity, is_6dof):
+        with torch.cuda.device(xyz.device):
+            return _PrepareGaussians._forward(ctx, xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity,
+                                              is_6dof)
+
+    @staticmethod
+    def _forward(ctx, xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity, is_6dof):
         lib = _lib.load()
         N = int(xyz.shape[0])
         dev = xyz.device
@@ -41,6 +47,11 @@ class _PrepareGaussians(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g_means, g_opac, g_scales, g_rots):
+        with torch.cuda.device(ctx.saved_tensors[0].device):
+            return _PrepareGaussians._backward(ctx, g_means, g_opac, g_scales, g_rots)
+
+    @staticmethod
+    def _backward(ctx, g_means, g_opac, g_scales, g_rots):
         lib = _lib.load()
         xyz, d_xyz, scaling, rotation, opacity = ctx.saved_tensors
         N = int(xyz.shape[0])

@@ -149,7 +149,8 @@ int d3g_image_loss_backward(int32_t C, int32_t H, int32_t W, const float* img, c
 
 /* Fused multi-tensor Adam step: what `optimizer.step()` of scene/gaussian_model.py:136 and
  * scene/deform_model.py:295,337 (torch.optim.Adam, betas (0.9, 0.999), eps 1e-15, optional weight_decay, no amsgrad)
- * does for every parameter, in one launch.  `step` is the 1-based step count AFTER this update (torch increments
+ * does for every parameter, in one launch.  betas / eps are the Python doubles torch uses (1 - beta and the bias
+ * corrections are formed in double).  `step` is the 1-based step count AFTER this update (torch increments
  * before use); all pointers are fp32 device arrays of `numel` elements, updated in place. */
 typedef struct d3g_adam_tensor {
   float* param;
@@ -161,7 +162,7 @@ typedef struct d3g_adam_tensor {
   float weight_decay;
   int64_t step;
 } d3g_adam_tensor;
-int d3g_adam_step(int32_t n_tensors, const d3g_adam_tensor* tensors, float beta1, float beta2, float eps,
+int d3g_adam_step(int32_t n_tensors, const d3g_adam_tensor* tensors, double beta1, double beta2, double eps,
                   void* stream);
 
 /* `simple_knn._C.distCUDA2` (submodules/simple-knn/spatial.cu:15-26 -> SimpleKNN::knn, simple_knn.cu:185-221; caller
@@ -242,6 +243,9 @@ typedef struct d3g_mlp_grads {
 int d3g_mlp_packed_bytes(const d3g_mlp_config* cfg, size_t* bytes);
 int d3g_mlp_workspace_bytes(const d3g_mlp_config* cfg, int64_t rows, int32_t save_for_backward,
                             size_t* bytes);
+/* The same for the time-batched calls below (n_times blocks of n_points rows). */
+int d3g_mlp_workspace_bytes_times(const d3g_mlp_config* cfg, int64_t n_points, int32_t n_times,
+                                  int32_t save_for_backward, size_t* bytes);
 
 /* Re-pack the parameters into the swizzled tile images the kernels stream (call after every
  * optimizer step; ~4 MB, one small kernel). */
@@ -257,14 +261,35 @@ int d3g_mlp_forward(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp
                     void* workspace, int32_t save_for_backward, float* d_xyz, float* d_rot,
                     float* d_scale, void* stream);
 
+/* The multi-timestamp form of DeformModel.step (scene/deform_model.py:260-273 loops over the columns of
+ * time_emb[N,T] and stacks the results): n_times time values, each applied to the same n_points points, in ONE
+ * persistent launch (the weights are shared across timestamps).  t_values: [n_times] device.  Outputs are
+ * [n_times, n_points, .] contiguous (torch.stack order).  workspace: d3g_mlp_workspace_bytes_times. */
+int d3g_mlp_forward_times(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp_params* p,
+                          int64_t n_points, int32_t n_times, const float* xyz, const float* t_values,
+                          void* workspace, int32_t save_for_backward, float* d_xyz, float* d_rot,
+                          float* d_scale, void* stream);
+
 /* Backward.  dL_d* are the cotangents of forward's outputs (NULL = zero).  Parameter gradients are
- * accumulated into `g`.  dL_dxyz [rows,3] and dL_dt [rows] may be NULL (every reference call site
- * passes xyz.detach(), scene/deform_model.py callers train.py:208, train_baseline.py:115). */
+ * accumulated into `g`.  dL_dxyz [rows,3] and dL_dt may be NULL (the baseline call sites pass xyz.detach(),
+ * train.py:208, train_baseline.py:115; the ODE function of utils/time_utils.py:392-438 needs both).  dL_dt is
+ * [rows] (one value per row) when forward was given per-row times (t_stride != 0) and a single float (the sum
+ * over the rows) when t_stride == 0.  Per-row time values are fully supported (scene/deform_model.py:260-273
+ * accepts any [N,T]; train_baseline.py:110-115 passes a materialised [N,1]): whether the rows actually differ
+ * is decided on the device, so N copies of one value still take the shared-t fast path. */
 int d3g_mlp_backward(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp_params* p,
                      int64_t rows, const float* xyz, const float* t, int64_t t_stride,
                      void* workspace, const float* dL_dxyz_out, const float* dL_drot,
                      const float* dL_dscale, const d3g_mlp_grads* g, float* dL_dxyz, float* dL_dt,
                      void* stream);
+
+/* Backward of d3g_mlp_forward_times.  Cotangents are [n_times, n_points, .]; dL_dxyz [n_points,3] (nullable)
+ * receives the sum over the time blocks, dL_dt [n_times] (nullable) the sum over the points of each block. */
+int d3g_mlp_backward_times(const d3g_mlp_config* cfg, const void* packed, const d3g_mlp_params* p,
+                           int64_t n_points, int32_t n_times, const float* xyz, const float* t_values,
+                           void* workspace, const float* dL_dxyz_out, const float* dL_drot,
+                           const float* dL_dscale, const d3g_mlp_grads* g, float* dL_dxyz, float* dL_dt,
+                           void* stream);
 
 /* Synchronises `stream` and returns the kernels' status word (0 = ok, non-zero = an internal
  * pipeline wait timed out, i.e. a bug).  Tests and debug mode call it; the hot path does not. */

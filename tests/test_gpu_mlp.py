@@ -100,12 +100,23 @@ def _relF(a, b):
     return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30)
 
 
-def _check_backward(net, ws, rows, ref, x, t, gd, gr, gs, baseline):
+def _check_backward(net, ws, rows, ref, x, t, gd, gr, gs, baseline, input_grads=None):
     masks = net.read_activation_masks(ws, rows)
     ref.forward(x, t)
-    g_same = ref.backward(gd, gr if baseline else None, gs if baseline else None, masks=masks)
+    g_same = ref.backward(gd, gr if baseline else None, gs if baseline else None, masks=masks,
+                          want_input_grads=input_grads is not None)
     g_own = ref.backward(gd, gr if baseline else None, gs if baseline else None)
     bad, loose_bad = {}, {}
+    if input_grads is not None:   # dL/dxyz [N,3], dL/dt [N,1] (or its sum for a shared t)
+        gx, gt = input_grads
+        e, em = _relF(gx, g_same["_x"]), _rel(gx, g_same["_x"])
+        if not (e < MAXTOL and em < 2 * MAXTOL):
+            bad["_x"] = (e, em)
+        if gt is not None:
+            want = g_same["_t"] if np.asarray(gt).size == rows else g_same["_t"].sum()
+            e = _relF(np.asarray(gt).reshape(-1), np.asarray(want).reshape(-1))
+            if not e < MAXTOL:
+                bad["_t"] = e
     for k, p in net.named_parameters():
         if k not in g_same:
             assert p.grad is None or torch.all(p.grad == 0), k
@@ -132,16 +143,26 @@ def _check_backward(net, ws, rows, ref, x, t, gd, gr, gs, baseline):
     assert flips < 2e-3 * rows * 2048, flips
 
 
-@pytest.mark.parametrize("fname,is_blender,is_6dof,baseline,head_scale", CASES[:4])
-def test_backward_matches_reference_golden(fname, is_blender, is_6dof, baseline, head_scale):
+# how the time tensor reaches forward(): "expand" = fid.expand(N,1) (stride 0, train.py:207); "materialised" = the
+# contiguous [N,1] that `time_input + ast_noise` produces at train_baseline.py:110-115 (N copies of one value for
+# blender scenes); "rows" = genuinely different values per row (scene/deform_model.py:260-273 accepts any [N,T])
+@pytest.mark.parametrize("t_form", ["expand", "materialised"])
+@pytest.mark.parametrize("fname,is_blender,is_6dof,baseline,head_scale", CASES)
+def test_backward_matches_reference_golden(fname, is_blender, is_6dof, baseline, head_scale, t_form):
     deform = pkg("deform")
     z = np.load(os.path.join(GOLD, fname))
     params = mlp_ref.seeded_params(int(z["seed"]), is_blender, is_6dof, head_scale=head_scale)
     net = _make_net(is_blender, is_6dof, baseline, params)
-    x = torch.tensor(z["x"]).cuda()
-    t = torch.tensor(z["t"]).cuda()
-    if bool(np.all(z["t"] == z["t"][0])):
-        t = t[:1].expand(x.shape[0], 1)
+    x = torch.tensor(z["x"]).cuda().requires_grad_(True)
+    uniform = bool(np.all(z["t"] == z["t"][0]))
+    if uniform and t_form == "expand":
+        t_leaf = torch.tensor(z["t"][:1]).cuda().requires_grad_(True)
+        t = t_leaf.expand(x.shape[0], 1)
+    elif t_form == "expand":
+        pytest.skip("fixture has per-row times")
+    else:
+        t_leaf = torch.tensor(z["t"]).cuda().requires_grad_(True)
+        t = t_leaf + 0
     d_xyz, rot, sc = net(x, t)
     loss = (d_xyz * torch.tensor(z["g_dxyz"]).cuda()).sum()
     if baseline:
@@ -149,7 +170,102 @@ def test_backward_matches_reference_golden(fname, is_blender, is_6dof, baseline,
     loss.backward()
     ref = mlp_ref.DeformRef(params, is_blender, is_6dof, baseline, dtype=np.float64)
     _check_backward(net, deform._FusedDeform.last_ws, x.shape[0], ref, z["x"], z["t"], z["g_dxyz"],
-                    z["g_rot"] if baseline else None, z["g_scale"] if baseline else None, baseline)
+                    z["g_rot"] if baseline else None, z["g_scale"] if baseline else None, baseline,
+                    input_grads=(x.grad.cpu().numpy(), t_leaf.grad.cpu().numpy()))
+    # and against the reference's own autograd (fp64) for the inputs
+    assert _relF(x.grad.cpu().numpy(), z["grad_x"]) < LOOSE
+    net.check_status()
+
+
+def test_train_baseline_call_site():
+    """train_baseline.py:110-115 literally: time_input = fid.unsqueeze(0).expand(N,-1); deform.step(xyz.detach(),
+    time_input + ast_noise) followed by backward (ast_noise = 0 for blender scenes)."""
+    deform = pkg("deform")
+    N = 1000
+    model = deform.DeformModelBaseline(is_blender=True)
+    xyz = torch.randn(N, 3, device="cuda").requires_grad_(True)
+    fid = torch.tensor([0.42], device="cuda")
+    time_input = fid.unsqueeze(0).expand(N, -1)
+    d_xyz, d_rot, d_sc = model.step(xyz.detach(), time_input + 0)
+    (d_xyz.sum() + d_rot.sum() + d_sc.sum()).backward()
+    g_mat = {k: p.grad.clone() for k, p in model.deform.named_parameters()}
+    for p in model.deform.parameters():
+        p.grad = None
+    d_xyz2, d_rot2, d_sc2 = model.step(xyz.detach(), time_input)
+    assert torch.equal(d_xyz, d_xyz2) and torch.equal(d_rot, d_rot2)
+    (d_xyz2.sum() + d_rot2.sum() + d_sc2.sum()).backward()
+    for k, p in model.deform.named_parameters():
+        assert _rel(g_mat[k].cpu(), p.grad.cpu()) < 1e-5, k
+    model.deform.check_status()
+
+
+def test_times_launch_matches_loop():
+    """DeformModel.step with T expanded fids: one launch for all T timestamps (forward_times) against the reference's
+    per-column loop (scene/deform_model.py:266-272), outputs and parameter / input gradients."""
+    deform = pkg("deform")
+    N, T = 777, 3
+    params = mlp_ref.seeded_params(9)
+    rng = np.random.default_rng(2)
+    x_np = rng.uniform(-1.3, 1.3, size=(N, 3)).astype(np.float32)
+    fids = torch.tensor([0.1, 0.5, 0.9], device="cuda")
+    cot = torch.tensor(rng.standard_normal((T, N, 3)).astype(np.float32)).cuda()
+    res = {}
+    for mode in ("loop", "times"):
+        model = deform.DeformModel(is_blender=True)
+        model.deform.load_state_dict({k: torch.tensor(v) for k, v in params.items()})
+        x = torch.tensor(x_np).cuda().requires_grad_(True)
+        f = fids.clone().requires_grad_(True)
+        te = f.unsqueeze(0).expand(N, T)
+        if mode == "loop":
+            te = te + 0      # materialised -> the per-column path
+        d_xyz, rl, sl = model.step(x, te)
+        assert d_xyz.shape == (T, N, 3) and len(rl) == T and len(sl) == T
+        (d_xyz * cot).sum().backward()
+        res[mode] = (d_xyz.detach().cpu().numpy(), x.grad.cpu().numpy(), f.grad.cpu().numpy(),
+                     {k: p.grad.cpu().numpy() for k, p in model.deform.named_parameters() if p.grad is not None})
+        model.deform.check_status()
+    assert np.array_equal(res["loop"][0], res["times"][0])
+    assert _rel(res["times"][1], res["loop"][1]) < 1e-5
+    assert _rel(res["times"][2], res["loop"][2]) < 1e-4
+    for k in res["loop"][3]:
+        assert _rel(res["times"][3][k], res["loop"][3][k]) < 1e-4, k
+
+
+def test_adam_step_reaches_the_kernels():
+    """After optimizer.step() (fused Adam writes through raw pointers) the next forward must run on the NEW weights:
+    the packed weight images are keyed on the parameters' version counters.  Compared with a torch network driven
+    by torch.optim.Adam on identical data."""
+    deform = pkg("deform")
+    params = mlp_ref.seeded_params(4)
+    N = 512
+    x = torch.rand(N, 3, device="cuda") * 2 - 1
+    t = torch.full((1, 1), 0.3, device="cuda").expand(N, 1)
+    cot = torch.randn(N, 3, device="cuda")
+    model = deform.DeformModelBaseline(is_blender=True)
+    model.deform.load_state_dict({k: torch.tensor(v) for k, v in params.items()})
+    args = type("A", (), dict(position_lr_init=2e-4, position_lr_final=2e-6, position_lr_delay_mult=0.01,
+                              deform_lr_max_steps=40000))()
+    model.train_setting(args)
+    model.update_learning_rate(1)
+    ref = mlp_ref.DeformRef(params, dtype=np.float64)
+    outs = []
+    for it in range(3):
+        d_xyz, _, _ = model.step(x, t)
+        outs.append(d_xyz.detach().cpu().numpy())
+        (d_xyz * cot).sum().backward()
+        model.optimizer.step()
+        model.optimizer.zero_grad()
+    assert not np.array_equal(outs[0], outs[1]) and not np.array_equal(outs[1], outs[2])
+    # the kernels saw exactly the weights the optimizer now holds
+    cur = {k: v.detach().cpu().numpy() for k, v in model.deform.state_dict().items()}
+    ref2 = mlp_ref.DeformRef(cur, dtype=np.float64)
+    with torch.no_grad():
+        d_now, _, _ = model.step(x, t)
+    want, _, _ = ref2.forward(x.cpu().numpy(), np.array([[0.3]]))
+    assert _rel(d_now.cpu().numpy(), want) < TOL
+    # and that really is a different function from the initial one
+    init, _, _ = ref.forward(x.cpu().numpy(), np.array([[0.3]]))
+    assert _rel(d_now.cpu().numpy(), init) > 10 * TOL
 
 
 def test_backward_large_vs_oracle():
