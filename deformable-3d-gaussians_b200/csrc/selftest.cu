@@ -3,6 +3,7 @@
 // Called from tests/ through d3g_selftest_umma; it exists so that a wrong descriptor bit shows up as
 // a small, localised GEMM failure instead of a wrong MLP.
 #include "common.cuh"
+#include "d3g_selftest.h"
 #include "umma.cuh"
 
 namespace d3g {
@@ -146,6 +147,127 @@ extern "C" int d3g_selftest_umma(int32_t mode, int32_t N, int32_t K, const float
   cudaFree(flag);
   if (e != cudaSuccess) return set_err(D3G_ERR_CUDA, "self-test failed: %s", cudaGetErrorString(e));
   if (h) return set_err(D3G_ERR_CUDA, "self-test: mbarrier wait timed out (protocol error)");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// kind::f16 self-test (fp16 operands, fp32 accumulation) through the 16-bit operand conventions of umma.cuh:
+//   mode 10: A,B K-major SW128 images in shared memory (A given [128,K], B given [N,K])
+//   mode 11: A in tensor memory, two consecutive k packed per 32-bit column (low half = even k), B K-major
+//   mode 12: A,B MN-major from [K,128] / [K,N] matrices stored with the SAME image formula (rows = k)
+// Inputs are fp32 arrays holding fp16-representable values.
+// ------------------------------------------------------------------------------------------------
+#include <cuda_fp16.h>
+namespace d3g {
+__global__ void __launch_bounds__(128, 1)
+selftest_f16_kernel(int mode, int N, int K, const float* __restrict__ A, const float* __restrict__ B,
+                    float* __restrict__ D, int* abort_flag) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_base_s;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + 32768;
+  const uint32_t a_panel = mode == 12 ? (uint32_t)K * 128u : 128u * 128u;
+  const uint32_t b_panel = mode == 12 ? (uint32_t)K * 128u : (uint32_t)N * 128u;
+  if (warp == 0) tmem_alloc(&tmem_base_s, 512);
+  if (tid == 0) { mbar_init(&bar, 1); fence_barrier_init(); }
+  if (mode == 12) {
+    for (int i = tid; i < K * 128; i += 128) {
+      int k = i / 128, m = i % 128;
+      *(__half*)(sA + img_off16(k, m, a_panel)) = __float2half_rn(A[(size_t)k * 128 + m]);
+    }
+    for (int i = tid; i < K * N; i += 128) {
+      int k = i / N, n = i % N;
+      *(__half*)(sB + img_off16(k, n, b_panel)) = __float2half_rn(B[(size_t)k * N + n]);
+    }
+  } else {
+    if (mode == 10)
+      for (int i = tid; i < 128 * K; i += 128) {
+        int r = i / K, c = i % K;
+        *(__half*)(sA + img_off16(r, c, a_panel)) = __float2half_rn(A[(size_t)r * K + c]);
+      }
+    for (int i = tid; i < N * K; i += 128) {
+      int r = i / K, c = i % K;
+      *(__half*)(sB + img_off16(r, c, b_panel)) = __float2half_rn(B[(size_t)r * K + c]);
+    }
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+  const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+  const uint32_t a_col0 = 256;
+  if (mode == 11) {
+    for (int c0 = 0; c0 < K; c0 += 32) {   // 32 k = 16 packed columns
+      uint32_t v[16];
+#pragma unroll
+      for (int j = 0; j < 16; j++) {
+        const __half2 h = __floats2half2_rn(A[(size_t)tid * K + c0 + 2 * j], A[(size_t)tid * K + c0 + 2 * j + 1]);
+        v[j] = *(const uint32_t*)&h;
+      }
+      tmem_st16(lane_addr + a_col0 + c0 / 2, v);
+    }
+    tmem_wait_st();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+  }
+  if (tid == 0) {
+    const uint32_t mn = mode == 12;
+    const uint32_t idesc = make_idesc_f16(128, N, mn, mn);
+    for (int k16 = 0; k16 < K / 16; k16++) {
+      if (mode == 12) {
+        const uint64_t ad = make_smem_desc_t(smem_u32(sA) + k16 * 2048, a_panel, 1024, 2u);
+        const uint64_t bd = make_smem_desc_t(smem_u32(sB) + k16 * 2048, b_panel, 1024, 2u);
+        umma_f16_ss(tmem_base, ad, bd, idesc, k16 > 0);
+      } else {
+        const uint64_t bd = make_smem_desc(smem_u32(sB) + (k16 / 4) * b_panel + (k16 % 4) * 32, 16, 1024);
+        if (mode == 11) umma_f16_ts(tmem_base, tmem_base + a_col0 + k16 * 8, bd, idesc, k16 > 0);
+        else umma_f16_ss(tmem_base, make_smem_desc(smem_u32(sA) + (k16 / 4) * a_panel + (k16 % 4) * 32, 16, 1024), bd, idesc, k16 > 0);
+      }
+    }
+    umma_commit(&bar);
+  }
+  bool ok = mbar_wait(&bar, 0, abort_flag);
+  tc_fence_after();
+  if (ok) {
+    for (int c0 = 0; c0 < N; c0 += 16) {
+      uint32_t v[16];
+      tmem_ld16(lane_addr + c0, v);
+      tmem_wait_ld();
+#pragma unroll
+      for (int j = 0; j < 16; j++)
+        if (c0 + j < N) D[(size_t)tid * N + c0 + j] = __uint_as_float(v[j]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, 512);
+}
+}  // namespace d3g
+
+extern "C" int d3g_selftest_umma_f16(int32_t mode, int32_t N, int32_t K, const float* A, const float* B, float* D,
+                                     void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (mode < 10 || mode > 12) return set_err(D3G_ERR_INVALID, "mode must be 10..12");
+  if (N < 16 || N % 16 || N > 256 || K < 16 || K > 128 || K % 16 || (mode == 11 && K % 32) || (mode == 12 && N % 64))
+    return set_err(D3G_ERR_INVALID, "unsupported f16 self-test shape N=%d K=%d", N, K);
+  int* flag = nullptr;
+  D3G_CUDA_TRY(cudaMalloc(&flag, sizeof(int)));
+  D3G_CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(int), stream));
+  size_t smem = 1024 + 32768 + 65536 + 1024;
+  D3G_CUDA_TRY(cudaFuncSetAttribute(selftest_f16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  selftest_f16_kernel<<<1, 128, smem, stream>>>(mode, N, K, A, B, D, flag);
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+  int h = 0;
+  if (e == cudaSuccess) e = cudaMemcpy(&h, flag, sizeof(int), cudaMemcpyDeviceToHost);
+  cudaFree(flag);
+  if (e != cudaSuccess) return set_err(D3G_ERR_CUDA, "f16 self-test failed: %s", cudaGetErrorString(e));
+  if (h) return set_err(D3G_ERR_CUDA, "f16 self-test: mbarrier wait timed out (protocol error)");
   return 0;
 }
 

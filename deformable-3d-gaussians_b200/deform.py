@@ -23,7 +23,17 @@ HEAD_WARP, HEAD_ROT, HEAD_SCALE = 1, 2, 4
 
 
 def _param_list(net):
-    """(name, tensor) in the fixed order of the C structs d3g_mlp_params / d3g_mlp_grads."""
+    """(name, tensor) in the fixed order of the C structs d3g_mlp_params / d3g_mlp_grads.  Cached on the module
+    (the Parameter objects survive .cuda() / load_state_dict(); _apply() drops the cache anyway)."""
+    cached = net.__dict__.get("_named_cache")
+    if cached is not None:
+        return cached
+    out = _param_list_uncached(net)
+    net.__dict__["_named_cache"] = out
+    return out
+
+
+def _param_list_uncached(net):
     out = []
     if net.is_blender:
         out += [("timenet0_w", net.timenet[0].weight), ("timenet0_b", net.timenet[0].bias),
@@ -229,6 +239,16 @@ class _DeformBase(nn.Module):
         self.fused_grad_accumulation = False
         self._pack_cache = None
         self._status_pending, self._status_host, self._status_next = [], None, 0
+
+    def _apply(self, fn, *a, **kw):
+        self.__dict__.pop("_named_cache", None)
+        self._pack_cache = None
+        return super()._apply(fn, *a, **kw)
+
+    def __setattr__(self, name, value):
+        if isinstance(value, (nn.Parameter, nn.Module)):
+            self.__dict__.pop("_named_cache", None)
+        super().__setattr__(name, value)
 
     # -- C-ABI plumbing --------------------------------------------------------------------------
     def _cfg(self):

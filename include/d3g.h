@@ -300,25 +300,6 @@ int d3g_mlp_read_status(const void* workspace, int32_t* status_host, void* strea
 int d3g_mlp_read_masks(const d3g_mlp_config* cfg, const void* workspace, int64_t rows, int32_t layer,
                        uint32_t* dst_host, void* stream);
 
-/* tcgen05 self-test used by tests/: D[128,N] = A[128,K] * B[N,K]^T through the exact smem/TMEM
- * operand conventions the MLP kernels use.  mode 0: A,B K-major from smem; 1: A from TMEM;
- * 2: A,B MN-major from smem (A given as [K,128], B as [K,N]); 3: A MN-major, B = ones (N = 16), i.e.
- * D[m,:] = sum_k A[k,m] (the bias-gradient trick). */
-int d3g_selftest_umma(int32_t mode, int32_t N, int32_t K, const float* A, const float* B, float* D,
-                      void* stream);
-
-/* Raw tcgen05 probe (tests / tools only): host-supplied operand images, one shared-memory descriptor
- * pair per MMA (start-address field relative to the image), host-supplied instruction descriptor.
- * D is [128,N].  The MMA list is issued `reps` times (reps > 1 is used to time instruction throughput). */
-int d3g_selftest_umma_raw(const void* a_img, uint32_t a_bytes, const void* b_img, uint32_t b_bytes,
-                          int32_t n_mma, const uint64_t* adesc, const uint64_t* bdesc, uint32_t idesc,
-                          int32_t N, float* D, int32_t reps, void* stream);
-
-/* Throughput probe: `reps` x 4 MMAs (M=128, N=256, K=8, kind::tf32) per CTA on `ctas` CTAs; mode 0 = A from
- * shared memory, 1 = A from tensor memory, 2/3 = the same with epilogue-like tcgen05.ld/st traffic from eight
- * other warps, 4 = A from tensor memory while eight warps spin on an mbarrier.  clk_out (device, int64[ctas]) receives the clocks from first issue to commit arrival. */
-int d3g_selftest_umma_clk(int32_t mode, int32_t reps, int32_t ctas, int64_t* clk_out, void* stream);
-
 #ifdef __cplusplus
 }
 #endif

@@ -18,7 +18,14 @@ def test_library_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(lib, name), name
     lib.d3g_version.restype = C.c_int
-    assert lib.d3g_version() >= 1
+    assert lib.d3g_version() >= 2
+    # the tcgen05 probes live behind their own test-only header, outside the product ABI
+    probes = open(os.path.join(ROOT, "include", "d3g_selftest.h")).read()
+    declared_t = set(re.findall(r"\b(d3g_[a-z0-9_]+)\s*\(", probes))
+    assert declared_t == set(_lib.TEST_EXPORTS), declared_t ^ set(_lib.TEST_EXPORTS)
+    assert not declared_t & declared
+    for name in declared_t:
+        assert hasattr(lib, name), name
 
 
 def test_size_queries_run_without_a_gpu():

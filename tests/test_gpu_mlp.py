@@ -113,8 +113,12 @@ def _check_backward(net, ws, rows, ref, x, t, gd, gr, gs, baseline, input_grads=
         if not (e < MAXTOL and em < 2 * MAXTOL):
             bad["_x"] = (e, em)
         if gt is not None:
-            want = g_same["_t"] if np.asarray(gt).size == rows else g_same["_t"].sum()
-            e = _relF(np.asarray(gt).reshape(-1), np.asarray(want).reshape(-1))
+            per_row = np.asarray(gt).size == rows
+            want = np.asarray(g_same["_t"] if per_row else g_same["_t"].sum()).reshape(-1)
+            # a shared t receives the SUM of the per-row terms: its natural scale is their l2 norm, not the
+            # (cancelling) sum itself
+            scale = np.linalg.norm(want) if per_row else max(abs(float(want[0])), np.linalg.norm(g_same["_t"]))
+            e = np.linalg.norm(np.asarray(gt, np.float64).reshape(-1) - want) / max(scale, 1e-30)
             if not e < MAXTOL:
                 bad["_t"] = e
     for k, p in net.named_parameters():
