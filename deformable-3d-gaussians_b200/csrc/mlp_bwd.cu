@@ -1,19 +1,27 @@
-// Deformation-MLP backward for sm_100a: input-gradient chain + weight gradients, both on tcgen05.
+// Deformation-MLP backward for sm_100a: input-gradient chain + weight gradients, both on tcgen05 (kind::f16 with
+// fp32 accumulation, mlp_common.cuh).
 //
 // Reference: autograd through DeformNetwork(.Baseline).forward, utils/time_utils.py:102-127 / :176-201
 // (8x256 trunk with the skip at layer 5, heads, optional exp_se3 of utils/rigid_utils.py:60-83).
 //
+// Range: gradients reach this code at any magnitude (a mean-reduced image loss puts them around 1e-7), which fp16
+// cannot hold.  mlp_amax_kernel takes the largest |cotangent| of the call; every kernel derives the same power of two
+// gscale from it, the chain runs on gscale * cotangent and the results are multiplied by 1/gscale (exact) on the way
+// out.  Values more than ~2^-20 below the largest cotangent of the call are flushed — far below the parity bar, which
+// is relative to each tensor's largest gradient.
+//
 // Kernel 1 (mlp_dgrad_kernel) — same persistent / warp-specialised shape as the forward: per 128-point
 //   tile the head cotangents are gathered (and pushed back through the se(3) map for is_6dof) into a
 //   shared-memory A operand, dH_7 = dOut * W_heads, then for l = 7..1: dZ_l = dH_l (.) relu'(h_l) is
-//   formed IN PLACE in tensor memory (tcgen05.ld -> mask -> tcgen05.st) and consumed as the TMEM A
-//   operand of dH_{l-1} = dZ_l * W_l.  Each dZ_l tile is also written to HBM as an MN-major wgrad image.
+//   formed IN PLACE in tensor memory (tcgen05.ld -> mask -> fp16 pack -> tcgen05.st) and consumed as the TMEM A
+//   operand of dH_{l-1} = dZ_l * (W_l hi + W_l lo) — the weights are split (their rounding error would be the same
+//   for every row and survive the sum over rows), dZ is not (its rounding is independent per row).  Each dZ_l tile is
+//   also written to HBM as a [point][feature] fp16 image.
 // Kernel 2 (mlp_wgrad_kernel) — dW_l = dZ_l^T * h_{l-1} is a GEMM whose K dimension is the points.
-//   Both operands are read as MN-major images straight from what forward / kernel 1 saved; CTA pairs
-//   split the 256 output features, the tile range is split-K over the pairs, partial sums leave TMEM
-//   through vector reductions (red.global.add.v4.f32) into the gradient tensors.  Bias gradients are
-//   column sums of the dZ stages taken by the otherwise idle epilogue warps (a 16-column ones-MMA was
-//   measured to cost as much tensor time as the 256-column one, tools/bench_umma.py).
+//   Both operands are read as MN-major images straight from what forward / kernel 1 saved; every CTA owns all 256
+//   outputs of its tile range (two M=128 accumulators), the tile range is split-K over the CTAs, partial sums leave
+//   TMEM through vector reductions (red.global.add.v4.f32) into the gradient tensors.  Bias gradients are
+//   column sums of the dZ stages taken by the otherwise idle epilogue warps.
 // Kernel 3 (mlp_finish_kernel) — head biases and the timenet (13->256->30) backward for a shared t.
 #include <math.h>
 #include <stdlib.h>
@@ -26,10 +34,9 @@ constexpr int kBwdNumStages = 5;
 constexpr int kBwdThreads = 320;
 
 struct BwdSmem {
-  static constexpr uint32_t dout = 0;                       // 16 KB K-major panel (32 columns)
+  static constexpr uint32_t dout = 0;                       // 16 KB K-major panel (64 columns, 16 used)
   static constexpr uint32_t stages = kPanelBytes;
-  static constexpr uint32_t store = stages + kBwdNumStages * kStageBytes;  // 8 warps x 4 KB bulk-store staging
-  static constexpr uint32_t headb = store + 8 * 4096;                      // 16 floats
+  static constexpr uint32_t headb = stages + kBwdNumStages * kStageBytes;  // 16 floats
   static constexpr uint32_t bars = headb + 64;
   static constexpr uint32_t total = bars + 256;
 };
@@ -49,6 +56,9 @@ struct MlpBwdArgs {
   uint8_t* dz_img;
   uint8_t* dout_img;
   float* headb_acc;      // [16] column sums of dOut
+  uint32_t* amax_bits;
+  const int* gain_e;
+  int gtarget;
   int* abort_flag;
 };
 
@@ -125,13 +135,38 @@ __device__ __forceinline__ void head_cotangent(const MlpBwdArgs& a, int64_t grow
   }
 }
 
+// largest |head cotangent| of the call (after the se(3) pull-back for 6-DoF): one thread per row
+__global__ void __launch_bounds__(256) mlp_amax_kernel(MlpBwdArgs a) {
+  float m = 0.f;
+  const int64_t total = (int64_t)(a.tiles / a.tpb) * a.rows;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int blk = (int)(i / a.rows);
+    const int64_t prow = i - (int64_t)blk * a.rows;
+    float ho[16], o[16];
+    if (a.is_6dof) {
+      const float4* h4 = (const float4*)(a.heads_out + ((size_t)blk * a.tpb * kRows + prow) * 16);
+      float4 h0 = h4[0], h1 = h4[1];
+      ho[0] = h0.x; ho[1] = h0.y; ho[2] = h0.z; ho[3] = h0.w; ho[4] = h1.x; ho[5] = h1.y;
+    }
+    head_cotangent(a, i, ho, o);
+#pragma unroll
+    for (int j = 0; j < 16; j++) m = fmaxf(m, fabsf(o[j]));
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
+  if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(a.amax_bits, __float_as_uint(m));
+}
+
+__device__ __forceinline__ void stg128b(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
 __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* sDout = smem + BwdSmem::dout;
   uint8_t* sStage = smem + BwdSmem::stages;
   float* sHeadB = (float*)(smem + BwdSmem::headb);
-  uint8_t* sStore = smem + BwdSmem::store;
   uint64_t* bars = (uint64_t*)(smem + BwdSmem::bars);
   uint64_t* full = bars;                      // [kBwdNumStages]
   uint64_t* empty = bars + kBwdNumStages;     // [kBwdNumStages]
@@ -177,39 +212,39 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
   } else if (warp == 9) {
     // ================= MMA issuer =================
     if (lane == 0) {
-      const uint32_t idesc256 = make_idesc_tf32(128, 256, 0, 0);
+      const uint32_t idesc256 = make_idesc_f16(128, 256, 0, 0);
       int s = 0;
       uint32_t ph = 0, d_ph = 0, a_ph = 0;
       bool ok = true;
       auto release = [&]() { umma_commit(&empty[s]); if (++s == kBwdNumStages) { s = 0; ph ^= 1; } };
       for (int tile = blockIdx.x; ok && tile < a.tiles; tile += gridDim.x) {
-        // step 0: dH_7 = dOut[128,16] * Wheads[16,256]  (A from shared memory, K = 16)
+        // step 0: dH_7 = dOut[128,16] * Wheads[16,256]  (A from shared memory, K = 16; W = hi + lo)
         if (!mbar_wait(dout_ready, d_ph, abort_flag)) { ok = false; break; }
         d_ph ^= 1;
         if (!mbar_wait(&full[s], ph, abort_flag)) { ok = false; break; }
         tc_fence_after();
         {
-          uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes);
-          uint32_t sa = smem_u32(sDout);
-#pragma unroll
-          for (int ks = 0; ks < 2; ks++)
-            umma_tf32_ss(tmem_base + 0, make_smem_desc(sa + ks * 32, 16, 1024), make_smem_desc(sb + ks * 32, 16, 1024),
-                         idesc256, ks != 0);
+          const uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes);
+          const uint64_t ad = make_smem_desc(smem_u32(sDout), 16, 1024);
+          umma_f16_ss(tmem_base + 0, ad, make_smem_desc(sb, 16, 1024), idesc256, 0u);
+          umma_f16_ss(tmem_base + 0, ad, make_smem_desc(sb + 64, 16, 1024), idesc256, 1u);
           release();
           umma_commit(acc_full);
         }
-        // steps 1..7: dH_{7-j} = dZ_{8-j} * W_{8-j}; A = TMEM half (j-1)&1, D = half j&1
+        // steps 1..7: dH_{7-j} = dZ_{8-j} * W_{8-j}; A = TMEM half (j-1)&1 (packed fp16), D = half j&1
         for (int j = 1; ok && j < 8; j++) {
           const uint32_t d_col = (j & 1) * 256, a_col = ((j - 1) & 1) * 256;
           for (int kc = 0; ok && kc < 8; kc++) {
             if (!mbar_wait(&a_ready[kc], a_ph, abort_flag)) { ok = false; break; }
             if (!mbar_wait(&full[s], ph, abort_flag)) { ok = false; break; }
             tc_fence_after();
-            uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes);
+            const uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes);
+            const uint32_t ta = tmem_base + a_col + kc * 32;
 #pragma unroll
-            for (int ks = 0; ks < 4; ks++)
-              umma_tf32_ts(tmem_base + d_col, tmem_base + a_col + kc * 32 + ks * 8,
-                           make_smem_desc(sb + ks * 32, 16, 1024), idesc256, (kc | ks) != 0);
+            for (int ks = 0; ks < 2; ks++) {
+              umma_f16_ts(tmem_base + d_col, ta + ks * 8, make_smem_desc(sb + ks * 32, 16, 1024), idesc256, (kc | ks) != 0);
+              umma_f16_ts(tmem_base + d_col, ta + ks * 8, make_smem_desc(sb + 64 + ks * 32, 16, 1024), idesc256, 1u);
+            }
             release();
           }
           a_ph ^= 1;
@@ -224,12 +259,14 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
     const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
     uint32_t acc_ph = 0;
     bool ok = true;
+    const GradScales G = grad_scales(*a.amax_bits, a.gtarget, a.gain_e);
+    const float gs = G.gs;
     for (int tile = blockIdx.x; ok && tile < a.tiles; tile += gridDim.x) {
       const int blk = tile / a.tpb;
       const int64_t prow = (int64_t)(tile - blk * a.tpb) * kRows + row;
       const bool live = prow < a.rows;
       const int64_t grow = (int64_t)blk * a.rows + prow;   // row of the [blocks, rows, .] cotangents
-      // ---- head cotangents -> shared A panel + HBM wgrad image; column sums for the head biases ----
+      // ---- head cotangents (x gscale, fp16) -> shared A panel + HBM image; column sums for the head biases ----
       if (chalf == 0) {
         float o[16];
         if (live) {
@@ -244,27 +281,18 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
 #pragma unroll
           for (int j = 0; j < 16; j++) o[j] = 0.f;
         }
-        uint32_t u[16];
+        uint32_t u[8];
 #pragma unroll
-        for (int j = 0; j < 16; j++) u[j] = to_tf32(o[j]);
+        for (int j = 0; j < 8; j++) u[j] = pack2(o[2 * j] * gs, o[2 * j + 1] * gs);
+        uint8_t* dst = a.dout_img + (size_t)tile * kDoutBytes + row * 128;
 #pragma unroll
-        for (int g = 0; g < 4; g++)
-          *(uint4*)(sDout + row * 128 + ((g ^ (row & 7)) << 4)) = make_uint4(u[4 * g], u[4 * g + 1], u[4 * g + 2], u[4 * g + 3]);
-        uint8_t* dst = a.dout_img + (size_t)tile * kDoutBytes + (row >> 5) * 4096 + (row & 31) * 128;
-#pragma unroll
-        for (int g = 0; g < 4; g++) {
-          uint4* d4 = (uint4*)(dst + ((g ^ (row & 3)) << 5));
-          if (g < 2) {
-            d4[0] = make_uint4(u[8 * g], u[8 * g + 1], u[8 * g + 2], u[8 * g + 3]);
-            d4[1] = make_uint4(u[8 * g + 4], u[8 * g + 5], u[8 * g + 6], u[8 * g + 7]);
-          } else {
-            d4[0] = make_uint4(0, 0, 0, 0);
-            d4[1] = make_uint4(0, 0, 0, 0);
-          }
+        for (int g = 0; g < 2; g++) {
+          sts128(smem_u32(sDout) + row * 128 + ((g ^ (row & 7)) << 4), u[4 * g], u[4 * g + 1], u[4 * g + 2], u[4 * g + 3]);
+          stg128b(dst + ((g ^ (row & 7)) << 4), u[4 * g], u[4 * g + 1], u[4 * g + 2], u[4 * g + 3]);
         }
 #pragma unroll
         for (int j = 0; j < 16; j++) {
-          float sum = __uint_as_float(u[j]);
+          float sum = o[j];
 #pragma unroll
           for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
           if (lane == 0) atomicAdd(&sHeadB[j], sum);
@@ -285,6 +313,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
         acc_ph ^= 1;
         tc_fence_after();
         const uint32_t half = (j & 1) * 256;
+        const float mul = G.step_mul[j];
 #pragma unroll
         for (int i = 0; i < 4; i++) {
           const int c = chalf + 2 * i;
@@ -292,45 +321,29 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
           tmem_ld32(lane_addr + half + c * 32, v);
           tmem_wait_ld();
           const uint32_t bits = mbits[i];
+          uint32_t o[16];
 #pragma unroll
-          for (int k = 0; k < 32; k++) v[k] = ((bits >> k) & 1u) ? tf32_rna_bits(v[k]) : 0u;
+          for (int k = 0; k < 32; k += 2) {
+            const float x0 = (bits & (1u << k)) ? __uint_as_float(v[k]) * mul : 0.f;
+            const float x1 = (bits & (2u << k)) ? __uint_as_float(v[k + 1]) * mul : 0.f;
+            o[k >> 1] = pack2(x0, x1);
+          }
           if (j < 7) {
-            tmem_st32(lane_addr + half + c * 32, v);
+            tmem_st16(lane_addr + half + c * 32, o);
             tmem_wait_st();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&a_ready[c]);
           }
-          // dZ block (32 rows x 128 B, contiguous in the wgrad image): staged in shared memory in the same
-          // swizzled layout and written by the bulk-copy engine as one 4 KB store
-          uint8_t* stg = sStore + (warp << 12);
-          if (lane == 0) bulk_wait_read<0>();
-          __syncwarp();
-          const bool swap = (lane >> 2) & 1;
-          const uint32_t line = smem_u32(stg) + lane * 128 + (swap ? 16 : 0);
+          // dZ -> [point][feature] image: 64 bytes = four 16-byte chunks of this thread's row inside panel c/2
+          uint8_t* dst = a.dz_img + ((size_t)l * a.tiles + tile) * kHBytes + (size_t)(c >> 1) * kPanelBytes + row * 128;
 #pragma unroll
-          for (int j8 = 0; j8 < 4; j8++) {
-            const uint32_t d = line + ((j8 ^ (lane & 3)) << 5);
-            // two straight-line variants (the lane quads diverge once) instead of 32 value selects
-            if (swap) {
-              sts128(d, v[8 * j8 + 4], v[8 * j8 + 5], v[8 * j8 + 6], v[8 * j8 + 7]);
-              sts128(d ^ 16u, v[8 * j8], v[8 * j8 + 1], v[8 * j8 + 2], v[8 * j8 + 3]);
-            } else {
-              sts128(d, v[8 * j8], v[8 * j8 + 1], v[8 * j8 + 2], v[8 * j8 + 3]);
-              sts128(d ^ 16u, v[8 * j8 + 4], v[8 * j8 + 5], v[8 * j8 + 6], v[8 * j8 + 7]);
-            }
-          }
-          fence_proxy_async();
-          __syncwarp();
-          if (lane == 0) {
-            bulk_s2g(a.dz_img + ((size_t)l * a.tiles + tile) * kHBytes + (size_t)q * 32768 + c * 4096, stg, 4096);
-            bulk_commit();
-          }
+          for (int g = 0; g < 4; g++)
+            stg128b(dst + (((4 * (c & 1) + g) ^ (row & 7)) << 4), o[4 * g], o[4 * g + 1], o[4 * g + 2], o[4 * g + 3]);
         }
       }
       tc_fence_before();
     }
-    if (lane == 0) bulk_wait_all<0>();
   }
   tc_fence_before();
   __syncthreads();
@@ -340,23 +353,28 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
 
 // ================================================================================================
 // Kernel 2: weight gradients.  One work item = one (A image set, B image set) GEMM over all tiles.
+// A stage holds 64 points: A = dZ slice [4 feature panels][64 rows][128 B] (32 KB), B = activation slice
+// [N/64 panels][64 rows][128 B]; both are MN-major SWIZZLE_128B operands (LBO = 8 KB panel stride, SBO = 1 KB).
 // ================================================================================================
 constexpr int kWgStages = 3;
-constexpr uint32_t kWgABytes = 32768;                 // 32 points x 256 features (both halves of the outputs)
-constexpr uint32_t kWgBBytes = 32768;                 // 32 points x up to 256 features
+constexpr int kWgPoints = 64;                         // points per stage
+constexpr uint32_t kWgPanel = kWgPoints * 128;        // 8 KB: one 64-feature panel of a stage
+constexpr uint32_t kWgABytes = 4 * kWgPanel;          // 64 points x 256 features (both halves of the outputs)
+constexpr uint32_t kWgBBytes = 4 * kWgPanel;          // 64 points x up to 256 features
 constexpr uint32_t kWgStageBytes = kWgABytes + kWgBBytes;
 constexpr int kWgThreads = 192;                       // warp 0 producer, 1 MMA, 2..5 epilogue
 constexpr int kWgItems = 10;
 
 struct WgItem {
-  const uint8_t* a_img;   // [tiles] x 128 KB images of 256 features (dz_l, or h_7 for the heads)
+  const uint8_t* a_img;   // [tiles] x 64 KB images of 256 features (dz_l, or h_7 for the heads)
   const uint8_t* b_img;   // [tiles] x b_tile_bytes
-  uint32_t b_tile_bytes;  // 131072 (h), 49152 (pe), 16384 (dout)
-  uint32_t b_chunk_bytes; // bytes of one 32-point chunk = (N/32)*4096
-  int N;                  // 256, 96 or 32
-  int bias;               // accumulate dZ^T * ones into columns 256..271
+  uint32_t b_tile_bytes;  // 65536 (h), 32768 (pe), 16384 (dout)
+  int b_panels;           // 64-feature panels of B to load: 4, 2 or 1
+  int N;                  // 256, 96 or 16
+  int bias;               // column sums of the A stages -> bias gradient
   int kind;               // 0: trunk layer (dW[o][col0+i]), 1: heads (transposed scatter)
-  int cost;               // relative cost per tile: KB moved per 32-point stage (the kernel is HBM-bound)
+  int layer;              // trunk: whose dZ image A is (its scale 2^E_layer is undone on the way out); -1: heads
+  int cost;               // relative cost per tile: KB moved (the kernel is HBM-bound)
   float* dW;              // trunk: gradient of linear.l.weight
   int ld, col0, ncols;
   float* db;              // trunk: gradient of linear.l.bias (or NULL)
@@ -370,6 +388,9 @@ struct MlpWgradArgs {
   int tiles;
   int tpb;                // tiles per time block: db_fresh is kept per block ([blocks][2][256])
   float* head_dw[16];     // heads: gradient row pointers (NULL where the head is not evaluated)
+  const uint32_t* amax_bits;
+  const int* gain_e;
+  int gtarget;
   int* abort_flag;
 };
 
@@ -392,9 +413,8 @@ __device__ __forceinline__ void red_add_v4f(float* addr, float x, float y, float
 __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint8_t* sStage = smem;                                   // kWgStages x 48 KB
-  uint8_t* sOnes = smem + kWgStages * kWgStageBytes;        // 2 KB: 16 rows x 128 B of 1.0f
-  uint64_t* bars = (uint64_t*)(sOnes + 2048);
+  uint8_t* sStage = smem;                                   // kWgStages x 64 KB
+  uint64_t* bars = (uint64_t*)(smem + kWgStages * kWgStageBytes);
   uint64_t* full = bars;
   uint64_t* empty = bars + kWgStages;
   uint64_t* acc_full = bars + 2 * kWgStages;
@@ -404,7 +424,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   volatile int* abort_flag = a.abort_flag;
   // every CTA owns all 256 outputs of its tile range (two M=128 accumulators = all 512 TMEM columns): the B stage
-  // is then read once per point instead of once per CTA of a pair (a third less L2->SM traffic)
+  // is then read once per point instead of once per CTA of a pair
   const int pair = blockIdx.x, pairs = gridDim.x;
 
   if (tid == 0) {
@@ -423,7 +443,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
   for (int it = 0; it < a.n_items; it++) total += (int64_t)a.items[it].cost * a.tiles;
 
   if (warp == 0) {
-    // ================= producer: one 32-point chunk of A (this CTA's half) and B per stage ==========
+    // ================= producer: 64 points of A (all 256 features) and B per stage ==========
     if (lane == 0) {
       int s = 0;
       uint32_t ph = 0;
@@ -437,14 +457,18 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
         for (int tile = t0; ok && tile < t1; tile++) {
           const uint8_t* pa = w.a_img + (size_t)tile * kHBytes;
           const uint8_t* pb = w.b_img + (size_t)tile * w.b_tile_bytes;
-          for (int ch = 0; ch < 4; ch++) {
+          for (int ch = 0; ch < kRows / kWgPoints; ch++) {
             if (!mbar_wait(&empty[s], ph ^ 1, abort_flag)) { ok = false; break; }
             uint8_t* dst = sStage + (size_t)s * kWgStageBytes;
             if (a.dbg & 1) { mbar_arrive(&full[s]); }
             else {
-              mbar_arrive_expect_tx(&full[s], kWgABytes + w.b_chunk_bytes);
-              bulk_g2s(dst, pa + (size_t)ch * 32768, kWgABytes, &full[s]);
-              bulk_g2s(dst + kWgABytes, pb + (size_t)ch * w.b_chunk_bytes, w.b_chunk_bytes, &full[s]);
+              mbar_arrive_expect_tx(&full[s], kWgABytes + (uint32_t)w.b_panels * kWgPanel);
+#pragma unroll
+              for (int pn = 0; pn < 4; pn++)
+                bulk_g2s(dst + pn * kWgPanel, pa + (size_t)pn * kPanelBytes + (size_t)ch * kWgPanel, kWgPanel, &full[s]);
+              for (int pn = 0; pn < w.b_panels; pn++)
+                bulk_g2s(dst + kWgABytes + pn * kWgPanel, pb + (size_t)pn * kPanelBytes + (size_t)ch * kWgPanel, kWgPanel,
+                         &full[s]);
             }
             if (++s == kWgStages) { s = 0; ph ^= 1; }
           }
@@ -464,22 +488,23 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
         wg_segment(a, pair, pairs, it, base, total, t0, t1);
         base += (int64_t)w.cost * a.tiles;
         if (t0 >= t1) continue;
-        const uint32_t idesc = make_idesc_tf32(128, (uint32_t)w.N, 1, 1);
+        const uint32_t idesc = make_idesc_f16(128, (uint32_t)w.N, 1, 1);
         // the previous segment's accumulator must have been drained
         if (!mbar_wait(acc_empty, e_ph ^ 1, abort_flag)) { ok = false; break; }
         tc_fence_after();
         uint32_t first = 1;
         for (int tile = t0; ok && tile < t1; tile++) {
-          for (int ch = 0; ch < 4; ch++) {
+          for (int ch = 0; ch < kRows / kWgPoints; ch++) {
             if (!mbar_wait(&full[s], ph, abort_flag)) { ok = false; break; }
             tc_fence_after();
             const uint32_t sa = smem_u32(sStage + (size_t)s * kWgStageBytes), sb = sa + kWgABytes;
 #pragma unroll
-            for (int k8 = 0; k8 < 4; k8++) {
+            for (int k16 = 0; k16 < kWgPoints / 16; k16++) {
               if (a.dbg & 2) break;
-              const uint64_t bd = make_smem_desc_mn(sb + k8 * 1024);
-              umma_tf32_ss(tmem_base, make_smem_desc_mn(sa + k8 * 1024), bd, idesc, first ? 0u : 1u);
-              umma_tf32_ss(tmem_base + 256, make_smem_desc_mn(sa + 16384 + k8 * 1024), bd, idesc, first ? 0u : 1u);
+              const uint64_t bd = make_smem_desc_t(sb + k16 * 2048, kWgPanel, 1024, 2u);
+              umma_f16_ss(tmem_base, make_smem_desc_t(sa + k16 * 2048, kWgPanel, 1024, 2u), bd, idesc, first ? 0u : 1u);
+              umma_f16_ss(tmem_base + 256, make_smem_desc_t(sa + 2 * kWgPanel + k16 * 2048, kWgPanel, 1024, 2u), bd, idesc,
+                          first ? 0u : 1u);
               first = 0;
             }
             if (a.dbg & 8) mbar_arrive(&empty[s]); else umma_commit(&empty[s]);
@@ -498,43 +523,47 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
     int64_t base = 0;
     int s = 0;
     uint32_t ph = 0;
-    // bias gradients: thread f sums feature f of this CTA's half over the 32 points of every stage
-    // (CUDA cores; a 16-column "ones" MMA costs as much tensor time as the 256-column one)
-    const int f = (warp - 2) * 32 + lane;
-    const uint32_t f_off = (uint32_t)(f >> 5) * 4096u + (uint32_t)(f & 7) * 4u, f_chunk = (uint32_t)(f & 31) >> 3;
+    const GradScales G = grad_scales(*a.amax_bits, a.gtarget, a.gain_e);
+    // bias gradients: thread j sums features 2j, 2j+1 over the 64 points of every A stage
+    const int f = 2 * ((warp - 2) * 32 + lane);
+    const uint32_t f_off = (uint32_t)(f >> 6) * kWgPanel + (uint32_t)(f & 7) * 2u, f_chunk = (uint32_t)(f & 63) >> 3;
     for (int it = 0; ok && it < a.n_items; it++) {
       const WgItem& w = a.items[it];
       int t0, t1;
       wg_segment(a, pair, pairs, it, base, total, t0, t1);
       base += (int64_t)w.cost * a.tiles;
       if (t0 >= t1) continue;
+      const float gs_inv = w.layer >= 0 ? G.dz_inv[w.layer] : G.gs_inv;
       float bsum = 0.f, bsum1 = 0.f;
       int cur_blk = t0 / a.tpb;
+      auto flush_bias = [&]() {
+        if (w.db) { atomicAdd(w.db + f, bsum * gs_inv); atomicAdd(w.db + f + 1, bsum1 * gs_inv); }
+        if (w.db_fresh) {
+          atomicAdd(w.db_fresh + (size_t)cur_blk * 512 + f, bsum * gs_inv);
+          atomicAdd(w.db_fresh + (size_t)cur_blk * 512 + f + 1, bsum1 * gs_inv);
+        }
+        bsum = bsum1 = 0.f;
+      };
       for (int tile = t0; ok && tile < t1; tile++) {
         if (w.bias && tile / a.tpb != cur_blk) {   // next time block: flush this block's bias sums
-          if (w.db) { atomicAdd(w.db + f, bsum); atomicAdd(w.db + 128 + f, bsum1); }
-          if (w.db_fresh) {
-            atomicAdd(w.db_fresh + (size_t)cur_blk * 512 + f, bsum);
-            atomicAdd(w.db_fresh + (size_t)cur_blk * 512 + 128 + f, bsum1);
-          }
-          bsum = bsum1 = 0.f;
+          flush_bias();
           cur_blk = tile / a.tpb;
         }
-        for (int ch = 0; ch < 4; ch++) {
+        for (int ch = 0; ch < kRows / kWgPoints; ch++) {
           if (!mbar_wait(&full[s], ph, abort_flag)) { ok = false; break; }
           if (w.bias) {
-            const uint8_t* sa = sStage + (size_t)s * kWgStageBytes + f_off;
+            const uint32_t sa = smem_u32(sStage + (size_t)s * kWgStageBytes) + f_off;
             float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, acc3 = 0.f;
 #pragma unroll
-            for (int p = 0; p < 32; p += 2) {
-              const uint32_t o0 = p * 128 + ((f_chunk ^ (p & 3)) << 5), o1 = (p + 1) * 128 + ((f_chunk ^ ((p + 1) & 3)) << 5);
-              acc0 += *(const float*)(sa + o0);
-              acc1 += *(const float*)(sa + o1);
-              acc2 += *(const float*)(sa + 16384 + o0);   // feature f + 128
-              acc3 += *(const float*)(sa + 16384 + o1);
+            for (int p = 0; p < kWgPoints; p += 2) {
+              uint32_t u0, u1;
+              asm volatile("ld.shared.b32 %0, [%1];" : "=r"(u0) : "r"(sa + p * 128 + ((f_chunk ^ (p & 7)) << 4)));
+              asm volatile("ld.shared.b32 %0, [%1];" : "=r"(u1) : "r"(sa + (p + 1) * 128 + ((f_chunk ^ ((p + 1) & 7)) << 4)));
+              const float2 x0 = __half22float2(*(const __half2*)&u0), x1 = __half22float2(*(const __half2*)&u1);
+              acc0 += x0.x; acc1 += x0.y; acc2 += x1.x; acc3 += x1.y;
             }
-            bsum += acc0 + acc1;
-            bsum1 += acc2 + acc3;
+            bsum += acc0 + acc2;
+            bsum1 += acc1 + acc3;
           }
           __syncwarp();
           if (lane == 0) mbar_arrive(&empty[s]);
@@ -546,42 +575,41 @@ __global__ void __launch_bounds__(kWgThreads, 1) mlp_wgrad_kernel(MlpWgradArgs a
       f_ph ^= 1;
       tc_fence_after();
       for (int hh = 0; hh < 2; hh++) {
-      const int o = hh * 128 + q * 32 + lane;
-      const uint32_t lane_addr = lane_addr0 + hh * 256;
-      for (int c0 = 0; c0 < w.N; c0 += 32) {
-        uint32_t v[32];
-        tmem_ld32(lane_addr + c0, v);
-        tmem_wait_ld();
-        if (a.dbg & 4) continue;
+        const int o = hh * 128 + q * 32 + lane;
+        const uint32_t lane_addr = lane_addr0 + hh * 256;
         if (w.kind == 0) {
-          float* dst = w.dW + (size_t)o * w.ld + w.col0 + c0;
+          for (int c0 = 0; c0 < w.N; c0 += 32) {
+            uint32_t v[32];
+            tmem_ld32(lane_addr + c0, v);
+            tmem_wait_ld();
+            if (a.dbg & 4) continue;
+            float* dst = w.dW + (size_t)o * w.ld + w.col0 + c0;
 #pragma unroll
-          for (int j = 0; j < 8; j++) {
-            float* p4 = dst + 4 * j;
-            if (c0 + 4 * j + 3 < w.ncols && (((uintptr_t)p4) & 15) == 0) {
-              red_add_v4f(p4, __uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
-                          __uint_as_float(v[4 * j + 3]));
-            } else {
-#pragma unroll
-              for (int e = 0; e < 4; e++)
-                if (c0 + 4 * j + e < w.ncols) atomicAdd(p4 + e, __uint_as_float(v[4 * j + e]));
+            for (int j = 0; j < 8; j++) {
+              float* p4 = dst + 4 * j;
+              const float x0 = __uint_as_float(v[4 * j]) * gs_inv, x1 = __uint_as_float(v[4 * j + 1]) * gs_inv,
+                          x2 = __uint_as_float(v[4 * j + 2]) * gs_inv, x3 = __uint_as_float(v[4 * j + 3]) * gs_inv;
+              if (c0 + 4 * j + 3 < w.ncols && (((uintptr_t)p4) & 15) == 0) {
+                red_add_v4f(p4, x0, x1, x2, x3);
+              } else {
+                if (c0 + 4 * j < w.ncols) atomicAdd(p4, x0);
+                if (c0 + 4 * j + 1 < w.ncols) atomicAdd(p4 + 1, x1);
+                if (c0 + 4 * j + 2 < w.ncols) atomicAdd(p4 + 2, x2);
+                if (c0 + 4 * j + 3 < w.ncols) atomicAdd(p4 + 3, x3);
+              }
             }
           }
         } else {
           // heads: D[in-feature o][head j] -> d(head weight row j)[o]
+          uint32_t v[16];
+          tmem_ld16(lane_addr, v);
+          tmem_wait_ld();
 #pragma unroll
           for (int j = 0; j < 16; j++)
-            if (a.head_dw[j]) atomicAdd(a.head_dw[j] + o, __uint_as_float(v[j]));
+            if (a.head_dw[j]) atomicAdd(a.head_dw[j] + o, __uint_as_float(v[j]) * gs_inv);
         }
       }
-      }
-      if (w.bias) {
-        if (w.db) { atomicAdd(w.db + f, bsum); atomicAdd(w.db + 128 + f, bsum1); }
-        if (w.db_fresh) {
-          atomicAdd(w.db_fresh + (size_t)cur_blk * 512 + f, bsum);
-          atomicAdd(w.db_fresh + (size_t)cur_blk * 512 + 128 + f, bsum1);
-        }
-      }
+      if (w.bias) flush_bias();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(acc_empty);
@@ -702,7 +730,7 @@ __global__ void __launch_bounds__(256) mlp_finish_kernel(MlpFinishArgs a) {
 //   per-row timenet backward 30 <- 256 <- 13 and dL/dt                                 (mlp_timenet_rows_kernel)
 // ================================================================================================
 struct MlpDpeArgs {
-  const uint8_t* dz0;   // dZ images of layer 0 and layer 5, [tiles] x 128 KB
+  const uint8_t* dz0;   // gscale * dZ images (fp16) of layer 0 and layer 5, [tiles] x 64 KB
   const uint8_t* dz5;
   const float* w0;      // [256, pe_dim]
   const float* w5;      // [256, pe_dim + 256]
@@ -711,50 +739,56 @@ struct MlpDpeArgs {
   float* dpe;           // [tiles*128, 96]
   int skip_if_uniform;  // nothing downstream needs dPE when the time values turned out equal
   const int* nonuniform;
+  const uint32_t* amax_bits;
+  const int* gain_e;
+  int gtarget;
 };
 
 __global__ void __launch_bounds__(256) mlp_dpe_kernel(MlpDpeArgs a) {
-  __shared__ __align__(16) uint8_t sA[4 * 4096];   // 128 points x 32 features, raw wgrad-image blocks
-  __shared__ __align__(16) float sB[32 * 96];
+  __shared__ __align__(16) uint8_t sA[kPanelBytes];   // 128 points x 64 features, one image panel as stored
+  __shared__ __align__(16) float sB[64 * 96];
   if (a.skip_if_uniform && !*a.nonuniform) return;
+  const GradScales G = grad_scales(*a.amax_bits, a.gtarget, a.gain_e);
   const int tid = threadIdx.x, rg = tid >> 4, cgp = tid & 15;
   for (int tile = blockIdx.x; tile < a.tiles; tile += gridDim.x) {
-    float acc[8][6];
+    float acc[8][6], tot[8][6];
 #pragma unroll
     for (int i = 0; i < 8; i++)
 #pragma unroll
-      for (int j = 0; j < 6; j++) acc[i][j] = 0.f;
+      for (int j = 0; j < 6; j++) tot[i][j] = 0.f;
     for (int src = 0; src < 2; src++) {
+#pragma unroll
+      for (int i = 0; i < 8; i++)
+#pragma unroll
+        for (int j = 0; j < 6; j++) acc[i][j] = 0.f;
       const uint8_t* img = (src ? a.dz5 : a.dz0) + (size_t)tile * kHBytes;
       const float* W = src ? a.w5 : a.w0;
       const int ld = src ? a.pe_dim + 256 : a.pe_dim;
-      for (int kc = 0; kc < 8; kc++) {
+      for (int kc = 0; kc < 4; kc++) {
         __syncthreads();
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-          const int idx = tid + i * 256;            // float4 index, 256 per 4 KB block
-          const int pc = idx >> 8, within = idx & 255;
-          ((float4*)sA)[idx] = *(const float4*)(img + ((size_t)pc * 8 + kc) * 4096 + (size_t)within * 16);
-        }
-        for (int idx = tid; idx < 32 * 96; idx += 256) {
+        for (int i = 0; i < 4; i++)
+          ((float4*)sA)[tid + i * 256] = *(const float4*)(img + (size_t)kc * kPanelBytes + (size_t)(tid + i * 256) * 16);
+        for (int idx = tid; idx < 64 * 96; idx += 256) {
           const int k = idx / 96, c = idx - k * 96;
-          sB[idx] = c < a.pe_dim ? W[(size_t)(kc * 32 + k) * ld + c] : 0.f;
+          sB[idx] = c < a.pe_dim ? W[(size_t)(kc * 64 + k) * ld + c] : 0.f;
         }
         __syncthreads();
-#pragma unroll
-        for (int k4 = 0; k4 < 8; k4++) {
-          float av[8][4];
+#pragma unroll 2
+        for (int k8 = 0; k8 < 8; k8++) {
+          float av[8][8];
 #pragma unroll
           for (int i = 0; i < 8; i++) {
             const int p = rg * 8 + i;
-            // img_off_mn inside the 32-feature panel: 32-byte chunk (k/8) ^ (p&3), 16-byte half (k%8)/4
-            const float4 v = *(const float4*)(sA + (p >> 5) * 4096 + (p & 31) * 128 + ((((k4 >> 1)) ^ (p & 3)) << 5) +
-                                              ((k4 & 1) << 4));
-            av[i][0] = v.x; av[i][1] = v.y; av[i][2] = v.z; av[i][3] = v.w;
+            const uint4 u = *(const uint4*)(sA + p * 128 + ((k8 ^ (p & 7)) << 4));
+            const float2 f0 = __half22float2(*(const __half2*)&u.x), f1 = __half22float2(*(const __half2*)&u.y),
+                         f2 = __half22float2(*(const __half2*)&u.z), f3 = __half22float2(*(const __half2*)&u.w);
+            av[i][0] = f0.x; av[i][1] = f0.y; av[i][2] = f1.x; av[i][3] = f1.y;
+            av[i][4] = f2.x; av[i][5] = f2.y; av[i][6] = f3.x; av[i][7] = f3.y;
           }
 #pragma unroll
-          for (int kk = 0; kk < 4; kk++) {
-            const float* br = sB + (k4 * 4 + kk) * 96 + cgp * 6;
+          for (int kk = 0; kk < 8; kk++) {
+            const float* br = sB + (k8 * 8 + kk) * 96 + cgp * 6;
             const float2 b0 = *(const float2*)br, b1 = *(const float2*)(br + 2), b2 = *(const float2*)(br + 4);
             const float bv[6] = {b0.x, b0.y, b1.x, b1.y, b2.x, b2.y};
 #pragma unroll
@@ -764,12 +798,17 @@ __global__ void __launch_bounds__(256) mlp_dpe_kernel(MlpDpeArgs a) {
           }
         }
       }
+      const float inv = G.dz_inv[src ? 5 : 0];
+#pragma unroll
+      for (int i = 0; i < 8; i++)
+#pragma unroll
+        for (int j = 0; j < 6; j++) tot[i][j] = fmaf(acc[i][j], inv, tot[i][j]);
     }
 #pragma unroll
     for (int i = 0; i < 8; i++) {
       float* dst = a.dpe + ((size_t)tile * kRows + rg * 8 + i) * 96 + cgp * 6;
 #pragma unroll
-      for (int j = 0; j < 3; j++) *(float2*)(dst + 2 * j) = make_float2(acc[i][2 * j], acc[i][2 * j + 1]);
+      for (int j = 0; j < 3; j++) *(float2*)(dst + 2 * j) = make_float2(tot[i][2 * j], tot[i][2 * j + 1]);
     }
   }
 }
@@ -963,6 +1002,9 @@ static int mlp_backward_impl(const d3g_mlp_config* cfg, const void* packed, cons
   float* headb_acc = ws.scratch;
   float* db_fresh = ws.scratch + 16;
   int* nonuniform = ws.status + 1;
+  uint32_t* amax_bits = (uint32_t*)(ws.scratch + 16 + (size_t)sh.blocks * 512);
+  const int* gain_e = (const int*)((const uint8_t*)packed + kGainOff);
+  const int gtarget = 5;   // largest scaled head cotangent in [32, 64)
 
   // ---- kernel 1: input-gradient chain ----
   {
@@ -974,6 +1016,10 @@ static int mlp_backward_impl(const d3g_mlp_config* cfg, const void* packed, cons
     a.g_rot = (cfg->heads & 2) ? dL_drot : nullptr;
     a.g_scale = (cfg->heads & 4) ? dL_dscale : nullptr;
     a.dz_img = ws.dz_img; a.dout_img = ws.dout_img; a.headb_acc = headb_acc; a.abort_flag = ws.status;
+    a.amax_bits = amax_bits; a.gain_e = gain_e; a.gtarget = gtarget;
+    { ProfScope _p(PROF_MLP_FINISH, stream);
+      mlp_amax_kernel<<<2 * num_sms(), 256, 0, stream>>>(a);
+      D3G_LAUNCH_CHECK(0, stream); }
     size_t smem = BwdSmem::total + 1024;
     D3G_CUDA_TRY(cudaFuncSetAttribute(mlp_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = tiles < num_sms() ? tiles : num_sms();
@@ -990,30 +1036,31 @@ static int mlp_backward_impl(const d3g_mlp_config* cfg, const void* packed, cons
     memset(&a, 0, sizeof(a));
     { const char* e = getenv("D3G_WGRAD_DBG"); a.dbg = e ? atoi(e) : 0; }
     a.tiles = tiles; a.tpb = sh.tpb; a.abort_flag = ws.status;
+    a.amax_bits = amax_bits; a.gain_e = gain_e; a.gtarget = gtarget;
     const size_t layer_stride = (size_t)tiles * kHBytes;
     int nit = 0;
     auto trunk = [&](int l, const uint8_t* b_img, uint32_t b_tile, int N, int bias, int col0, int ncols, int cost) {
       WgItem& w = a.items[nit++];
       w.a_img = ws.dz_img + (size_t)l * layer_stride;
-      w.b_img = b_img; w.b_tile_bytes = b_tile; w.b_chunk_bytes = (uint32_t)(N / 32) * 4096u; w.N = N;
-      w.bias = bias; w.kind = 0; w.cost = cost;
+      w.b_img = b_img; w.b_tile_bytes = b_tile; w.b_panels = (N + 63) / 64; w.N = N;
+      w.bias = bias; w.kind = 0; w.layer = l; w.cost = cost;
       w.dW = g->linear_w[l]; w.ld = l == 0 ? pe_dim : (l == 5 ? pe_dim + 256 : 256); w.col0 = col0; w.ncols = ncols;
       w.db = bias ? g->linear_b[l] : nullptr;
       w.db_fresh = (bias && l == 0) ? db_fresh : ((bias && l == 5) ? db_fresh + 256 : nullptr);
     };
     for (int l = 7; l >= 1; l--)
-      trunk(l, ws.h_img + (size_t)(l - 1) * layer_stride, kHBytes, 256, 1, l == 5 ? pe_dim : 0, 256, 64);
-    trunk(0, ws.pe_img, kPeBytes, 96, 1, 0, pe_dim, 44);
-    trunk(5, ws.pe_img, kPeBytes, 96, 0, 0, pe_dim, 44);
+      trunk(l, ws.h_img + (size_t)(l - 1) * layer_stride, kHBytes, 256, 1, l == 5 ? pe_dim : 0, 256, 128);
+    trunk(0, ws.pe_img, kPeBytes, 96, 1, 0, pe_dim, 96);
+    trunk(5, ws.pe_img, kPeBytes, 96, 0, 0, pe_dim, 96);
     {
       WgItem& w = a.items[nit++];
       w.a_img = ws.h_img + (size_t)7 * layer_stride;
-      w.b_img = ws.dout_img; w.b_tile_bytes = kDoutBytes; w.b_chunk_bytes = 4096; w.N = 32;
-      w.bias = 0; w.kind = 1; w.cost = 36;
+      w.b_img = ws.dout_img; w.b_tile_bytes = kDoutBytes; w.b_panels = 1; w.N = 16;
+      w.bias = 0; w.kind = 1; w.layer = -1; w.cost = 80;
     }
     a.n_items = nit;
     for (int j = 0; j < 16; j++) a.head_dw[j] = hm.w[j] ? (float*)hm.w[j] + (size_t)hm.r[j] * 256 : nullptr;
-    size_t smem = (size_t)kWgStages * kWgStageBytes + 2048 + 256 + 1024;
+    size_t smem = (size_t)kWgStages * kWgStageBytes + 256 + 1024;
     D3G_CUDA_TRY(cudaFuncSetAttribute(mlp_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = num_sms();
     { ProfScope _p(PROF_MLP_WGRAD, stream);
@@ -1043,6 +1090,7 @@ static int mlp_backward_impl(const d3g_mlp_config* cfg, const void* packed, cons
     d.dz0 = ws.dz_img; d.dz5 = ws.dz_img + (size_t)5 * tiles * kHBytes;
     d.w0 = p->linear_w[0]; d.w5 = p->linear_w[5]; d.pe_dim = pe_dim; d.tiles = tiles; d.dpe = ws.dpe;
     d.skip_if_uniform = (!dL_dxyz && !want_dt_rows) ? 1 : 0; d.nonuniform = nonuniform;
+    d.amax_bits = amax_bits; d.gain_e = gain_e; d.gtarget = gtarget;
     { ProfScope _p(PROF_MLP_DPE, stream);
     mlp_dpe_kernel<<<tiles < 4 * num_sms() ? tiles : 4 * num_sms(), 256, 0, stream>>>(d);
     D3G_LAUNCH_CHECK(0, stream); }

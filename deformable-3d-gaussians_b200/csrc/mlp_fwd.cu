@@ -2,16 +2,18 @@
 //
 // Replaces DeformNetwork(.Baseline).forward, utils/time_utils.py:102-127 / :176-201: positional
 // encoding, 8x256 trunk with the skip at layer 5, heads and the optional se(3) exponential map run in
-// ONE persistent kernel.  Per 128-point tile:
-//   * the positional-encoding block (96 columns) is built in shared memory once and feeds layer 0 and
+// ONE persistent kernel.  Arithmetic is the split-fp16 scheme of mlp_common.cuh (three kind::f16 products per
+// k-step, fp32 accumulation: fp32-class accuracy).  Per 128-point tile:
+//   * the positional-encoding block (96 columns, hi | lo) is built in shared memory once and feeds layer 0 and
 //     the skip layer as an smem A operand;
 //   * every other activation lives ONLY in tensor memory: the fp32 accumulator of layer l (TMEM half
-//     l&1, 256 columns) is bias+ReLU'd in place by the epilogue warps (tcgen05.ld -> regs ->
-//     tcgen05.st, rounded to tf32) and is then consumed directly as the TMEM A operand of layer l+1,
-//     whose accumulator is the other half.  Activations never touch shared memory or HBM in inference;
-//   * weights stream from the packed image (L2-resident, 2 MB) through a 5-stage bulk-copy ring
-//     (cp.async.bulk + mbarrier expect_tx), 32 KB = 256 outputs x 32 k per stage;
-//   * the epilogue hands the next layer its A operand 32 columns at a time (8 mbarriers), so the MMA
+//     l&1, 256 columns) is bias+ReLU'd by the epilogue warps and written back IN PLACE as packed fp16 — the
+//     32 accumulator columns of a chunk become 16 columns of hi pairs + 16 columns of lo pairs — and is then
+//     consumed directly as the TMEM A operand of layer l+1, whose accumulator is the other half.
+//     Activations never touch shared memory or HBM in inference;
+//   * weights stream from the packed image (L2-resident, 2 MB) through a bulk-copy ring
+//     (cp.async.bulk + mbarrier expect_tx), 32 KB = 256 outputs x (32 k hi | 32 k lo) per stage;
+//   * the epilogue hands the next layer its A operand 32 features at a time (8 mbarriers), so the MMA
 //     of layer l+1 starts while the epilogue of layer l is still draining.
 // Warp roles (kEpiWarps = 8): 0-7 epilogue/PE (warp w owns TMEM lanes 32*(w&3).., column chunks of parity w>>2),
 // 8 weight producer, 9 MMA issuer + TMEM owner.
@@ -21,18 +23,15 @@
 
 namespace d3g {
 
-// 8 epilogue warps + a 4-stage ring measured faster than 16 warps + a 3-stage ring (0.308 vs 0.324 ms at 100k
-// points): the per-layer critical path is latency (tcgen05.ld -> bias/ReLU -> tcgen05.st -> mbarrier), not issue.
-constexpr int kNumStages = 4;
+constexpr int kNumStages = 5;
 constexpr int kEpiWarps = 8;                        // 2 per TMEM lane quarter, 4 column chunks each per layer
 constexpr int kFwdThreads = (kEpiWarps + 2) * 32;   // + weight producer + MMA issuer
 
 struct FwdSmem {
   // offsets inside dynamic shared memory (after 1024-alignment)
   static constexpr uint32_t pe = 0;
-  static constexpr uint32_t stages = kPeBytes;
-  static constexpr uint32_t store = stages + kNumStages * kStageBytes;   // one 4 KB bulk-store staging block per warp
-  static constexpr uint32_t bias = store + kEpiWarps * 4096;
+  static constexpr uint32_t stages = kPeSmemBytes;
+  static constexpr uint32_t bias = stages + kNumStages * kStageBytes;
   static constexpr uint32_t bars = bias + kBiasFloats * 4 + 64;  // 8-byte aligned
   static constexpr uint32_t total = bars + 256;
 };
@@ -61,8 +60,8 @@ struct MlpFwdArgs {
   int* abort_flag;
 };
 
-__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+__device__ __forceinline__ void stg128(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
 __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
@@ -71,7 +70,6 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
   uint8_t* sPE = smem + FwdSmem::pe;
   uint8_t* sStage = smem + FwdSmem::stages;
   float* sBias = (float*)(smem + FwdSmem::bias);
-  uint8_t* sStore = smem + FwdSmem::store;
   uint64_t* bars = (uint64_t*)(smem + FwdSmem::bars);
   uint64_t* full = bars;                   // [kNumStages]
   uint64_t* empty = bars + kNumStages;     // [kNumStages]
@@ -115,9 +113,11 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
     }
   } else if (warp == kEpiWarps + 1) {
     // ================= MMA issuer =================
+    // One k-chunk = 32 features: the B rows hold [32 k of Whi | 32 k of Wlo] (4 descriptors 32 B apart), the A
+    // side [hi | lo] likewise (16 + 16 packed TMEM columns, or 64 + 64 bytes of a shared-memory row).
     if (lane == 0) {
-      const uint32_t idesc256 = make_idesc_tf32(128, 256, 0, 0);
-      const uint32_t idesc16 = make_idesc_tf32(128, 16, 0, 0);
+      const uint32_t idesc256 = make_idesc_f16(128, 256, 0, 0);
+      const uint32_t idesc16 = make_idesc_f16(128, 16, 0, 0);
       int s = 0;
       uint32_t ph = 0, pe_ph = 0, a_ph = 0;
       bool ok = true;
@@ -127,32 +127,45 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
         if (!mbar_wait(pe_ready, pe_ph, abort_flag)) { ok = false; break; }
         pe_ph ^= 1;
         tc_fence_after();
-        // pe-fed part of a layer: A from shared memory (3 panels)
+        // pe-fed part of a layer: A from shared memory (3 chunks)
         auto pe_part = [&](uint32_t d_col) {
           for (int kc = 0; ok && kc < 3; kc++) {
             if (!wait_full()) { ok = false; break; }
             tc_fence_after();
-            uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes);
-            uint32_t sa = smem_u32(sPE) + kc * kPanelBytes;
+            const uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes);
+            const uint32_t sa = smem_u32(sPE) + kc * kPanelBytes;
 #pragma unroll
-            for (int ks = 0; ks < 4; ks++)
-              umma_tf32_ss(tmem_base + d_col, make_smem_desc(sa + ks * 32, 16, 1024),
-                           make_smem_desc(sb + ks * 32, 16, 1024), idesc256, (kc | ks) != 0);
+            for (int ks = 0; ks < 2; ks++) {   // hi * Whi
+              umma_f16_ss(tmem_base + d_col, make_smem_desc(sa + ks * 32, 16, 1024),
+                          make_smem_desc(sb + ks * 32, 16, 1024), idesc256, (kc | ks) != 0);
+            }
+#pragma unroll
+            for (int ks = 0; ks < 2; ks++) {   // lo * Whi, hi * Wlo
+              umma_f16_ss(tmem_base + d_col, make_smem_desc(sa + 64 + ks * 32, 16, 1024),
+                          make_smem_desc(sb + ks * 32, 16, 1024), idesc256, 1u);
+              umma_f16_ss(tmem_base + d_col, make_smem_desc(sa + ks * 32, 16, 1024),
+                          make_smem_desc(sb + 64 + ks * 32, 16, 1024), idesc256, 1u);
+            }
             release();
           }
         };
-        // h-fed part: A from tensor memory, handed over 32 columns at a time
+        // h-fed part: A from tensor memory, handed over 32 features at a time
         auto h_part = [&](uint32_t d_col, uint32_t a_col, bool accumulate_first) {
           for (int kc = 0; ok && kc < 8; kc++) {
             if (!mbar_wait(&a_ready[kc], a_ph, abort_flag)) { ok = false; break; }
             if (!wait_full()) { ok = false; break; }
             tc_fence_after();
-            uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes);
+            const uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes);
+            const uint32_t ta = tmem_base + a_col + kc * 32;
 #pragma unroll
-            for (int ks = 0; ks < 4; ks++)
-              umma_tf32_ts(tmem_base + d_col, tmem_base + a_col + kc * 32 + ks * 8,
-                           make_smem_desc(sb + ks * 32, 16, 1024), idesc256,
-                           (accumulate_first || (kc | ks) != 0) ? 1u : 0u);
+            for (int ks = 0; ks < 2; ks++)
+              umma_f16_ts(tmem_base + d_col, ta + ks * 8, make_smem_desc(sb + ks * 32, 16, 1024), idesc256,
+                          (accumulate_first || (kc | ks) != 0) ? 1u : 0u);
+#pragma unroll
+            for (int ks = 0; ks < 2; ks++) {
+              umma_f16_ts(tmem_base + d_col, ta + 16 + ks * 8, make_smem_desc(sb + ks * 32, 16, 1024), idesc256, 1u);
+              umma_f16_ts(tmem_base + d_col, ta + ks * 8, make_smem_desc(sb + 64 + ks * 32, 16, 1024), idesc256, 1u);
+            }
             release();
           }
           a_ph ^= 1;
@@ -173,18 +186,23 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
           umma_commit(acc_full);
         }
         if (!ok) break;
-        // heads: N = 16, A = h7 (half 1), D = half 0 columns 0..15, single 16 KB stage
+        // heads: N = 16, A = h7 (half 1), D = half 0 columns 0..15, single 16 KB stage of 8 chunks x 2 KB
         {
           bool have = false;
           for (int kc = 0; ok && kc < 8; kc++) {
             if (!mbar_wait(&a_ready[kc], a_ph, abort_flag)) { ok = false; break; }
             if (!have) { if (!wait_full()) { ok = false; break; } have = true; }
             tc_fence_after();
-            uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes) + kc * 2048;
+            const uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes) + kc * 2048;
+            const uint32_t ta = tmem_base + 256 + kc * 32;
 #pragma unroll
-            for (int ks = 0; ks < 4; ks++)
-              umma_tf32_ts(tmem_base + 0, tmem_base + 256 + kc * 32 + ks * 8,
-                           make_smem_desc(sb + ks * 32, 16, 1024), idesc16, (kc | ks) != 0);
+            for (int ks = 0; ks < 2; ks++)
+              umma_f16_ts(tmem_base + 0, ta + ks * 8, make_smem_desc(sb + ks * 32, 16, 1024), idesc16, (kc | ks) != 0);
+#pragma unroll
+            for (int ks = 0; ks < 2; ks++) {
+              umma_f16_ts(tmem_base + 0, ta + 16 + ks * 8, make_smem_desc(sb + ks * 32, 16, 1024), idesc16, 1u);
+              umma_f16_ts(tmem_base + 0, ta + ks * 8, make_smem_desc(sb + 64 + ks * 32, 16, 1024), idesc16, 1u);
+            }
           }
           if (!ok) break;
           a_ph ^= 1;
@@ -195,7 +213,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
     }
   } else {
     // ================= PE + epilogue warps (256 threads) =================
-    const int q = warp & 3, cg = warp >> 2, chalf = cg;   // cg: column-chunk group 0..3 (PE: groups 0,1 only)
+    const int q = warp & 3, cg = warp >> 2, chalf = cg;   // cg: column-chunk parity (PE: column half)
     const int row = q * 32 + lane;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
     uint32_t acc_ph = 0;
@@ -207,9 +225,10 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
       const bool live = prow < a.rows;
       const int64_t grow = (int64_t)blk * a.rows + prow;                  // row of the [blocks, rows, .] outputs
       // ---- positional encoding block: each row is built by two threads (columns 0..47 / 48..95) in
-      // registers, then written to shared memory (K-major SW128 image, A operand of layer 0 and of the
-      // skip layer) and, when saving for backward, to HBM as an MN-major wgrad image ----
-      if (cg < 2) {
+      // registers, split into fp16 hi / lo and written to shared memory (three k-chunks of [32 hi | 32 lo]
+      // K-major SW128 rows: A operand of layer 0 and of the skip layer) and, when saving for backward, to HBM
+      // as the hi-part [point][feature] image the weight gradient reads ----
+      {
         float x[3] = {0.f, 0.f, 0.f};
         if (live) { x[0] = a.xyz[3 * prow]; x[1] = a.xyz[3 * prow + 1]; x[2] = a.xyz[3 * prow + 2]; }
         float pe[48];
@@ -242,33 +261,32 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
 #pragma unroll
           for (int j = 0; j < 33; j++) pe[15 + j] = (live && j < a.t_dim) ? tf[j] : 0.f;
         }
-        uint32_t u[48];
+        uint32_t hi[24], lo[24];
 #pragma unroll
-        for (int j = 0; j < 48; j++) u[j] = to_tf32(pe[j]);
+        for (int j = 0; j < 24; j++) split2(pe[2 * j], pe[2 * j + 1], hi[j], lo[j]);
 #pragma unroll
-        for (int g = 0; g < 12; g++) {
-          const uint32_t col0 = chalf * 48 + 4 * g;
-          *(uint4*)(sPE + (col0 >> 5) * kPanelBytes + row * 128 + ((((col0 & 31u) >> 2) ^ (row & 7)) << 4)) =
-              make_uint4(u[4 * g], u[4 * g + 1], u[4 * g + 2], u[4 * g + 3]);
+        for (int g = 0; g < 6; g++) {   // groups of 8 columns = one 16-byte chunk of hi and one of lo
+          const uint32_t col0 = chalf * 48 + 8 * g;
+          const uint32_t base = smem_u32(sPE) + (col0 >> 5) * kPanelBytes + row * 128;
+          const uint32_t ch = (col0 & 31u) >> 3;
+          sts128(base + (((ch) ^ (row & 7)) << 4), hi[4 * g], hi[4 * g + 1], hi[4 * g + 2], hi[4 * g + 3]);
+          sts128(base + (((4 + ch) ^ (row & 7)) << 4), lo[4 * g], lo[4 * g + 1], lo[4 * g + 2], lo[4 * g + 3]);
         }
         if (a.save) {
-          uint8_t* dst = a.pe_img + (size_t)tile * kPeBytes + (row >> 5) * 3 * 4096 + (row & 31) * 128;
+          uint8_t* dst = a.pe_img + (size_t)tile * kPeBytes + row * 128;
 #pragma unroll
           for (int g = 0; g < 6; g++) {
             const uint32_t col0 = chalf * 48 + 8 * g;
-            uint4* d4 = (uint4*)(dst + (col0 >> 5) * 4096 + ((((col0 & 31u) >> 3) ^ (row & 3)) << 5));
-            d4[0] = make_uint4(u[8 * g], u[8 * g + 1], u[8 * g + 2], u[8 * g + 3]);
-            d4[1] = make_uint4(u[8 * g + 4], u[8 * g + 5], u[8 * g + 6], u[8 * g + 7]);
+            stg128(dst + (col0 >> 6) * kPanelBytes + ((((col0 & 63u) >> 3) ^ (row & 7)) << 4), hi[4 * g], hi[4 * g + 1],
+                   hi[4 * g + 2], hi[4 * g + 3]);
           }
         }
       }
-      if (cg < 2) {
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(pe_ready);
-      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(pe_ready);
 
-      // ---- trunk epilogues: bias + ReLU in place in TMEM, 32 columns at a time ----
+      // ---- trunk epilogues: bias + ReLU + hi/lo split in place in TMEM, 32 features at a time ----
       for (int l = 0; ok && l < 8; l++) {
         if (!mbar_wait(acc_full, acc_ph, abort_flag)) { ok = false; break; }
         acc_ph ^= 1;
@@ -287,50 +305,36 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
             const float4 b4 = lds128f(bl_s + 16 * j);
             bv[4 * j] = b4.x; bv[4 * j + 1] = b4.y; bv[4 * j + 2] = b4.z; bv[4 * j + 3] = b4.w;
           }
-          // bias + ReLU + tf32 rounding + activity bit in five instructions per element (1 FADD, 1 integer add,
-          // 3 logic/shift): x is rounded on its bit pattern, `neg` is its sign smeared over the word, the
-          // activation is r & ~neg and the mask bit ~neg & (1 << j).  (x == +0 counts as active with value 0.)
+          // z = acc * 2^-s + bias; `neg` is its sign smeared over the word: activation = z & ~neg, mask bit
+          // ~neg & (1 << j) (z == +0 counts as active with value 0); then the hi/lo split, two features per word
+          uint32_t o[32];
 #pragma unroll
-          for (int j = 0; j < 32; j++) {
-            const uint32_t r = __float_as_uint(__uint_as_float(v[j]) + bv[j]) + 0x1000u;
-            uint32_t neg;
-            asm("shr.s32 %0, %1, 31;" : "=r"(neg) : "r"(r));
-            asm("lop3.b32 %0, %1, %2, %3, 0x20;" : "=r"(v[j]) : "r"(r), "r"(neg), "r"(0xFFFFE000u));   // r & ~neg & C
-            asm("lop3.b32 %0, %0, %1, %2, 0xF2;" : "+r"(bits) : "r"(neg), "r"(1u << j));               // bits | (~neg & bit)
+          for (int j = 0; j < 32; j += 2) {
+            float r[2];
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+              const uint32_t zb = __float_as_uint(fmaf(__uint_as_float(v[j + e]), kWScaleInv, bv[j + e]));
+              uint32_t neg, rb;
+              asm("shr.s32 %0, %1, 31;" : "=r"(neg) : "r"(zb));
+              asm("lop3.b32 %0, %1, %2, %2, 0x30;" : "=r"(rb) : "r"(zb), "r"(neg));                      // z & ~neg
+              asm("lop3.b32 %0, %0, %1, %2, 0xF2;" : "+r"(bits) : "r"(neg), "r"(1u << (j + e)));          // bits | (~neg & bit)
+              r[e] = __uint_as_float(rb);
+            }
+            split2(r[0], r[1], o[j >> 1], o[16 + (j >> 1)]);
           }
-          tmem_st32(lane_addr + half + c * 32, v);
+          tmem_st32(lane_addr + half + c * 32, o);
           // hand the chunk to the MMA warp first, then save it for backward
           tmem_wait_st();
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&a_ready[c]);
           if (a.save) {
-            // The 32 rows x 128 B block this warp owns is contiguous in the wgrad image: build it in shared
-            // memory (same swizzled layout) and let the bulk-copy engine write it as one 4 KB store instead
-            // of 256 line-strided 16-byte stores per warp through L1.
-            uint8_t* stg = sStore + (warp << 12);
-            if (lane == 0) bulk_wait_read<0>();   // previous block has left the staging buffer
-            __syncwarp();
-            const bool swap = (lane >> 2) & 1;    // odd lane quads write the two 16 B halves in the other order
-            const uint32_t line = smem_u32(stg) + lane * 128 + (swap ? 16 : 0);
+            // hi part -> [point][feature] image: this thread's 32 features are 64 bytes = four 16-byte chunks of
+            // its row inside panel c/2
+            uint8_t* dst = a.h_img + ((size_t)l * a.tiles + tile) * kHBytes + (size_t)(c >> 1) * kPanelBytes + row * 128;
 #pragma unroll
-            for (int j8 = 0; j8 < 4; j8++) {
-              const uint32_t d = line + ((j8 ^ (lane & 3)) << 5);
-              // two straight-line variants (the lane quads diverge once) instead of 32 value selects
-              if (swap) {
-                sts128(d, v[8 * j8 + 4], v[8 * j8 + 5], v[8 * j8 + 6], v[8 * j8 + 7]);
-                sts128(d ^ 16u, v[8 * j8], v[8 * j8 + 1], v[8 * j8 + 2], v[8 * j8 + 3]);
-              } else {
-                sts128(d, v[8 * j8], v[8 * j8 + 1], v[8 * j8 + 2], v[8 * j8 + 3]);
-                sts128(d ^ 16u, v[8 * j8 + 4], v[8 * j8 + 5], v[8 * j8 + 6], v[8 * j8 + 7]);
-              }
-            }
-            fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) {
-              bulk_s2g(a.h_img + ((size_t)l * a.tiles + tile) * kHBytes + (size_t)q * 32768 + c * 4096, stg, 4096);
-              bulk_commit();
-            }
+            for (int g = 0; g < 4; g++)
+              stg128(dst + (((4 * (c & 1) + g) ^ (row & 7)) << 4), o[4 * g], o[4 * g + 1], o[4 * g + 2], o[4 * g + 3]);
             a.mask[(((size_t)l * a.tiles + tile) * 8 + c) * 128 + row] = bits;
           }
         }
@@ -347,7 +351,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
         float o[16];
         const float* bh = sBias + 8 * 256;
 #pragma unroll
-        for (int j = 0; j < 16; j++) o[j] = __uint_as_float(v[j]) + bh[j];
+        for (int j = 0; j < 16; j++) o[j] = fmaf(__uint_as_float(v[j]), kWScaleInv, bh[j]);
         if (a.save) {
           float4* dst = (float4*)(a.heads_out + ((size_t)tile * kRows + row) * 16);
 #pragma unroll
@@ -395,7 +399,6 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
       }
       tc_fence_before();
     }
-    if (lane == 0) bulk_wait_all<0>();
   }
   tc_fence_before();
   __syncthreads();
@@ -472,12 +475,14 @@ tfeat_kernel(int64_t rows_t, const float* __restrict__ t, int64_t t_stride, int 
   }
 }
 
-// Pack parameters into the streaming images (forward stages, biases, transposed backward stages).
+// Pack parameters into the streaming images (forward stages, biases, transposed backward stages).  A stage is
+// 256 rows x 128 B: bytes 0..63 of a row = fp16 hi parts of 32 consecutive k of W * 2^kWScaleLog2, bytes 64..127 =
+// the fp16 lo parts (W*2^s - hi), 16-byte chunks XOR-swizzled with (row & 7).  One thread per (stage, row, 8 k).
 __global__ void __launch_bounds__(256)
 pack_weights_kernel(d3g_mlp_config cfg, d3g_mlp_params p, uint8_t* __restrict__ packed) {
   const int pe_dim = cfg.is_blender ? 93 : 84;
   int gid = blockIdx.x * blockDim.x + threadIdx.x;
-  const int per_stage = 256 * 8;  // (row, 16-byte chunk)
+  const int per_stage = 256 * 4;  // (row, group of 8 k)
   const int n_fwd = kFwdStages * per_stage, n_bwd = kBwdStages * per_stage;
   auto head_src = [&](int h, const float*& w, const float*& b, int& r) {
     w = nullptr; b = nullptr; r = 0;
@@ -492,22 +497,28 @@ pack_weights_kernel(d3g_mlp_config cfg, d3g_mlp_params p, uint8_t* __restrict__ 
       else if (h < 13) { if (cfg.heads & 4) { w = p.scale_w; b = p.scale_b; r = h - 10; } }
     }
   };
+  // write 8 values as one hi chunk (j) and one lo chunk (4 + j) of row n at `row_base`
+  auto put = [&](uint8_t* row_base, int n, int j, const float (&v)[8]) {
+    uint32_t hi[4], lo[4];
+#pragma unroll
+    for (int e = 0; e < 4; e++) split2(v[2 * e] * kWScale, v[2 * e + 1] * kWScale, hi[e], lo[e]);
+    *(uint4*)(row_base + ((j ^ (n & 7)) << 4)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    *(uint4*)(row_base + (((4 + j) ^ (n & 7)) << 4)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+  };
   if (gid < n_fwd) {
-    int st = gid / per_stage, rem = gid % per_stage, n = rem >> 3, j = rem & 7;
+    int st = gid / per_stage, rem = gid % per_stage, n = rem >> 2, j = rem & 3;
     int layer, kp;
     fwd_stage_info(st, layer, kp);
-    uint32_t vals[4] = {0, 0, 0, 0};
-    uint8_t* dst;
+    float v[8];
     if (layer == 9) {
       if (n >= 16) return;
-      // heads stage: 8 k-panels of 16 rows inside one 16 KB stage; this thread handles all 8 panels
+      // heads stage: 8 k-chunks of 16 rows inside one 16 KB stage; this thread handles all 8 chunks
       const float* w; const float* b; int r;
       head_src(n, w, b, r);
       for (int kp2 = 0; kp2 < 8; kp2++) {
 #pragma unroll
-        for (int e = 0; e < 4; e++) vals[e] = w ? to_tf32(w[r * 256 + kp2 * 32 + j * 4 + e]) : 0u;
-        dst = packed + (size_t)st * kStageBytes + kp2 * 2048 + n * 128 + ((j ^ (n & 7)) << 4);
-        *(uint4*)dst = make_uint4(vals[0], vals[1], vals[2], vals[3]);
+        for (int e = 0; e < 8; e++) v[e] = w ? w[r * 256 + kp2 * 32 + j * 8 + e] : 0.f;
+        put(packed + (size_t)st * kStageBytes + kp2 * 2048 + n * 128, n, j, v);
       }
       return;
     }
@@ -517,40 +528,38 @@ pack_weights_kernel(d3g_mlp_config cfg, d3g_mlp_params p, uint8_t* __restrict__ 
     else if (layer == 5) { W = p.linear_w[5]; ld = pe_dim + 256; col0 = pe_dim; ncols = 256; }
     else { W = p.linear_w[layer]; ld = 256; col0 = 0; ncols = 256; }
 #pragma unroll
-    for (int e = 0; e < 4; e++) {
-      int c = kp * 32 + j * 4 + e;
-      vals[e] = c < ncols ? to_tf32(W[(size_t)n * ld + col0 + c]) : 0u;
+    for (int e = 0; e < 8; e++) {
+      int c = kp * 32 + j * 8 + e;
+      v[e] = c < ncols ? W[(size_t)n * ld + col0 + c] : 0.f;
     }
-    dst = packed + (size_t)st * kStageBytes + n * 128 + ((j ^ (n & 7)) << 4);
-    *(uint4*)dst = make_uint4(vals[0], vals[1], vals[2], vals[3]);
+    put(packed + (size_t)st * kStageBytes + n * 128, n, j, v);
     return;
   }
   gid -= n_fwd;
   if (gid < n_bwd) {
     // transposed images: row n = input feature, k = output feature (or head row)
-    int st = gid / per_stage, rem = gid % per_stage, n = rem >> 3, j = rem & 7;
+    int st = gid / per_stage, rem = gid % per_stage, n = rem >> 2, j = rem & 3;
     int layer, kp;
     bwd_stage_info(st, layer, kp);
-    uint32_t vals[4];
+    float v[8];
 #pragma unroll
-    for (int e = 0; e < 4; e++) {
-      int k = kp * 32 + j * 4 + e;
-      float v = 0.f;
+    for (int e = 0; e < 8; e++) {
+      int k = kp * 32 + j * 8 + e;
+      float x = 0.f;
       if (layer == 9) {
         if (k < 16) {
           const float* w; const float* b; int r;
           head_src(k, w, b, r);
-          if (w) v = w[r * 256 + n];
+          if (w) x = w[r * 256 + n];
         }
       } else if (layer == 5) {
-        v = p.linear_w[5][(size_t)k * (pe_dim + 256) + pe_dim + n];
+        x = p.linear_w[5][(size_t)k * (pe_dim + 256) + pe_dim + n];
       } else {
-        v = p.linear_w[layer][(size_t)k * 256 + n];
+        x = p.linear_w[layer][(size_t)k * 256 + n];
       }
-      vals[e] = to_tf32(v);
+      v[e] = x;
     }
-    uint8_t* dst = packed + kBwdOff + (size_t)st * kStageBytes + n * 128 + ((j ^ (n & 7)) << 4);
-    *(uint4*)dst = make_uint4(vals[0], vals[1], vals[2], vals[3]);
+    put(packed + kBwdOff + (size_t)st * kStageBytes + n * 128, n, j, v);
     return;
   }
   gid -= n_bwd;
@@ -563,6 +572,43 @@ pack_weights_kernel(d3g_mlp_config cfg, d3g_mlp_params p, uint8_t* __restrict__ 
       if (b) v = b[r];
     }
     ((float*)(packed + kBiasOff))[gid] = v;
+  }
+}
+
+// Backward gain exponents (mlp_common.cuh "Backward range management"): block 0..7 = trunk layer l (the h-fed
+// columns of its weight), block 8 = the evaluated heads.  e = -round(log2(rms gain of one chain step)).
+__global__ void __launch_bounds__(256) pack_gains_kernel(d3g_mlp_config cfg, d3g_mlp_params p, uint8_t* __restrict__ packed) {
+  __shared__ float red[8];
+  const int l = blockIdx.x, tid = threadIdx.x;
+  const int pe_dim = cfg.is_blender ? 93 : 84;
+  float acc = 0.f;
+  if (l < 8) {
+    const float* W = p.linear_w[l];
+    const int ld = l == 0 ? pe_dim : (l == 5 ? pe_dim + 256 : 256), col0 = l == 5 ? pe_dim : 0;
+    if (l > 0)
+      for (int i = tid; i < 256 * 256; i += 256) { const float w = W[(size_t)(i >> 8) * ld + col0 + (i & 255)]; acc += w * w; }
+  } else {
+    const float* rows[4] = {cfg.is_6dof ? p.branch_w_w : p.warp_w, cfg.is_6dof ? p.branch_v_w : nullptr,
+                            (cfg.heads & 2) ? p.rot_w : nullptr, (cfg.heads & 4) ? p.scale_w : nullptr};
+    const int nr[4] = {3, 3, 4, 3};
+    for (int h = 0; h < 4; h++)
+      if (rows[h])
+        for (int i = tid; i < nr[h] * 256; i += 256) { const float w = rows[h][i]; acc += w * w; }
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+  if ((tid & 31) == 0) red[tid >> 5] = acc;
+  __syncthreads();
+  if (tid == 0) {
+    float f2 = 0.f;
+    for (int i = 0; i < 8; i++) f2 += red[i];
+    // one chain step multiplies a random-direction gradient by ||W||_F / 16 (256 outputs), times sqrt(1/2) for the
+    // ReLU mask in the trunk
+    const float gain = sqrtf(f2 / 256.0f * (l < 8 ? 0.5f : 1.0f));
+    int e = 0;
+    if (gain > 0.f && gain < 3.0e38f) e = -(int)rintf(log2f(gain));
+    e = e < -12 ? -12 : (e > 12 ? 12 : e);
+    ((int*)(packed + kGainOff))[l] = e;
   }
 }
 
@@ -623,9 +669,11 @@ int d3g_mlp_pack_weights(const d3g_mlp_config* cfg, const d3g_mlp_params* p, voi
   if (cfg->is_6dof ? (!p->branch_w_w || !p->branch_v_w) : !p->warp_w)
     return set_err(D3G_ERR_INVALID, "warp head parameters missing");
   cudaStream_t stream = (cudaStream_t)stream_;
-  int total = (kFwdStages + kBwdStages) * 256 * 8 + kBiasFloats;
+  int total = (kFwdStages + kBwdStages) * 256 * 4 + kBiasFloats;
   { ProfScope _p(PROF_MLP_PACK, stream);
     pack_weights_kernel<<<(total + 255) / 256, 256, 0, stream>>>(*cfg, *p, (uint8_t*)packed);
+    D3G_LAUNCH_CHECK(0, stream);
+    pack_gains_kernel<<<9, 256, 0, stream>>>(*cfg, *p, (uint8_t*)packed);
   D3G_LAUNCH_CHECK(0, stream); }
   return 0;
 }
