@@ -1,7 +1,8 @@
 """GPU parity of the fused deformation MLP (through the C ABI) against the numpy oracle, which is itself
 pinned to the reference's torch module (tests/test_oracle_mlp.py).  Tolerance from BASELINE.json:
-deformation offsets and gradients within 1e-3 relative, measured per tensor as max|a-b| / max|b|
-(TF32 tensor-core inputs, fp32 accumulation)."""
+deformation offsets and gradients within 1e-3 relative, measured per tensor as max|a-b| / max|b|.
+The kernels run split-fp16 tensor-core arithmetic with fp32 accumulation (fp32-class accuracy: forward outputs
+measure ~2.5e-6)."""
 import os
 
 import numpy as np
@@ -14,6 +15,7 @@ from oracle import mlp_ref
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
 TOL = 1e-3
+FWD_TOL = 2e-5   # forward outputs: measured 2-3e-6
 
 
 def _rel(a, b):
@@ -49,10 +51,10 @@ def test_forward_matches_reference_golden(fname, is_blender, is_6dof, baseline, 
         t = t[:1].expand(x.shape[0], 1)  # the fid.expand(N,1) pattern -> stride 0
     with torch.no_grad():
         d_xyz, rot, sc = net(x, t)
-    assert _rel(d_xyz.cpu(), z["d_xyz"]) < TOL
+    assert _rel(d_xyz.cpu(), z["d_xyz"]) < FWD_TOL
     if baseline:
-        assert _rel(rot.cpu(), z["rot"]) < TOL
-        assert _rel(sc.cpu(), z["scale"]) < TOL
+        assert _rel(rot.cpu(), z["rot"]) < FWD_TOL
+        assert _rel(sc.cpu(), z["scale"]) < FWD_TOL
     else:
         assert rot == 0 and sc == 0
 
@@ -68,9 +70,10 @@ def test_forward_sizes_vs_oracle(N):
     ref = mlp_ref.DeformRef(params, dtype=np.float32 if N > 30000 else np.float64)
     sel = slice(None) if N <= 30000 else rng.choice(N, 20000, replace=False)
     rd, rr, rs = ref.forward(x[sel], np.array([[0.37]]))
-    assert _rel(d_xyz.cpu().numpy()[sel], rd) < TOL
-    assert _rel(rot.cpu().numpy()[sel], rr) < TOL
-    assert _rel(sc.cpu().numpy()[sel], rs) < TOL
+    tol = FWD_TOL if N <= 30000 else 1e-5 + FWD_TOL   # (the fp32 numpy oracle itself carries ~1e-6)
+    assert _rel(d_xyz.cpu().numpy()[sel], rd) < tol
+    assert _rel(rot.cpu().numpy()[sel], rr) < tol
+    assert _rel(sc.cpu().numpy()[sel], rs) < tol
 
 
 def test_state_dict_keys_and_param_count():
@@ -80,19 +83,23 @@ def test_state_dict_keys_and_param_count():
     assert set(net.state_dict().keys()) == set(mlp_ref.param_shapes(True, False).keys())
 
 
-# Gradient parity.  The forward runs on TF32 tensor cores (pre-activations accurate to ~5e-4 of their
-# scale), so a few ReLU units whose pre-activation sits within that noise of zero take the other branch
-# than in the fp64 oracle; each such flip perturbs the gradient of its row by O(1/sqrt(256)).  The checks
-# therefore are: (1) with the oracle evaluated on the GPU's own activation pattern every parameter
-# gradient agrees within the 1e-3 bar; (2) the two activation patterns differ only at units whose exact
-# pre-activation is within FLIP_BAND of zero relative to the layer's scale, and on < 0.2 % of units;
-# (3) against the oracle's own pattern the gradients still agree within LOOSE (measured ~3e-2 at N=20k,
-# up to 0.12 at N=500 where single flips are not averaged; DESIGN.md "MLP precision").
-# "Relative" for (1) is the relative l2 error ||a-b|| / ||b|| per tensor (bar 1e-3, measured ~3e-4); the
-# max-norm ratio max|a-b| / max|b| is reported against MAXTOL (the 8-layer TF32 chain measures 1.0-1.3e-3).
-FLIP_BAND = 4e-3
-LOOSE = 0.25
-MAXTOL = 2e-3
+# Gradient parity.  Two separate questions, checked separately:
+#  (1) ARITHMETIC: with the oracle evaluated on the GPU's own ReLU pattern (d3g_mlp_read_masks) every parameter /
+#      input gradient agrees within the 1e-3 bar, both as relative l2 error and as max|a-b| / max|b| (MAXTOL allows
+#      for the 257-row fixtures, where the fp16 rounding of single dZ elements is not averaged over many rows).
+#  (2) ReLU DECISIONS: pre-activations are accurate to ~1e-6 of their scale, so a unit flips against the fp64 oracle
+#      only when its exact pre-activation is within KNIFE_EDGE of zero — a few units in 10^7; an fp32 evaluation
+#      (the reference's own arithmetic) disagrees with fp64 on as many.  ONE such flip moves max|a-b|/max|b| of the
+#      affected weight row by several 1e-3 (the flipped unit's whole dz * h outer product appears or disappears in a
+#      257- or 20k-row sum), whatever the arithmetic; so when the patterns agree the UNMASKED comparison must meet the
+#      bar as well, and when they do not, every differing unit must be a knife-edge unit, there must be very few of
+#      them, and the unmasked gradients must still agree in relative l2 (FLIP_L2).
+# profiles/r2_mlp_parity_unmasked.json holds the measured numbers.
+KNIFE_EDGE = 2e-5      # |z| / max|z| of a unit allowed to take the other branch (measured: < 4e-6)
+FLIP_FRACTION = 2e-6   # of all units (measured 4e-7 at N = 20k; single-pass TF32 measured 1.5e-4)
+FLIP_L2 = 6e-3
+LOOSE = 0.05
+MAXTOL = 1.25e-3
 
 
 def _relF(a, b):
@@ -110,7 +117,7 @@ def _check_backward(net, ws, rows, ref, x, t, gd, gr, gs, baseline, input_grads=
     if input_grads is not None:   # dL/dxyz [N,3], dL/dt [N,1] (or its sum for a shared t)
         gx, gt = input_grads
         e, em = _relF(gx, g_same["_x"]), _rel(gx, g_same["_x"])
-        if not (e < MAXTOL and em < 2 * MAXTOL):
+        if not (e < TOL and em < MAXTOL):
             bad["_x"] = (e, em)
         if gt is not None:
             per_row = np.asarray(gt).size == rows
@@ -121,30 +128,31 @@ def _check_backward(net, ws, rows, ref, x, t, gd, gr, gs, baseline, input_grads=
             e = np.linalg.norm(np.asarray(gt, np.float64).reshape(-1) - want) / max(scale, 1e-30)
             if not e < MAXTOL:
                 bad["_t"] = e
-    for k, p in net.named_parameters():
-        if k not in g_same:
-            assert p.grad is None or torch.all(p.grad == 0), k
-            continue
-        assert p.grad is not None, k
-        e, em = _relF(p.grad.cpu(), g_same[k]), _rel(p.grad.cpu(), g_same[k])
-        # timenet sits behind the longest TF32 chain (8 trunk layers + the t-feature columns): measured
-        # 1.1e-3 on the 6-DoF fixture, so it is held to MAXTOL and listed as a known gap in DESIGN.md
-        tol = MAXTOL if k.startswith("timenet") else TOL
-        if not (e < tol and em < MAXTOL):
-            bad[k] = (e, em)
-        e2 = _rel(p.grad.cpu(), g_own[k])
-        if not e2 < LOOSE:
-            loose_bad[k] = e2
-    assert not bad, bad
-    assert not loose_bad, loose_bad
     flips = 0
     for l in range(8):
         z = ref.cache["z"][l]
         diff = masks[l] != (z > 0)
         flips += int(diff.sum())
         if diff.any():
-            assert np.abs(z[diff]).max() < FLIP_BAND * np.abs(z).max(), "layer %d flip outside the noise band" % l
-    assert flips < 2e-3 * rows * 2048, flips
+            assert np.abs(z[diff]).max() < KNIFE_EDGE * np.abs(z).max(), "layer %d flip outside the knife edge" % l
+    assert flips <= max(2, FLIP_FRACTION * rows * 2048), flips
+    for k, p in net.named_parameters():
+        if k not in g_same:
+            assert p.grad is None or torch.all(p.grad == 0), k
+            continue
+        assert p.grad is not None, k
+        e, em = _relF(p.grad.cpu(), g_same[k]), _rel(p.grad.cpu(), g_same[k])
+        if not (e < TOL and em < MAXTOL):
+            bad[k] = (e, em)
+        # against the oracle's own pattern: the same bar when the patterns agree, relative l2 otherwise
+        e2, em2 = _relF(p.grad.cpu(), g_own[k]), _rel(p.grad.cpu(), g_own[k])
+        if flips == 0:
+            if not (e2 < TOL and em2 < MAXTOL):
+                loose_bad[k] = (e2, em2)
+        elif not (e2 < FLIP_L2 and em2 < LOOSE):
+            loose_bad[k] = (e2, em2)
+    assert not bad, bad
+    assert not loose_bad, (flips, loose_bad)
 
 
 # how the time tensor reaches forward(): "expand" = fid.expand(N,1) (stride 0, train.py:207); "materialised" = the
