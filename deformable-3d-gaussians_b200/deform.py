@@ -45,8 +45,9 @@ def _param_list_uncached(net):
                 ("branch_v_w", net.branch_v.weight), ("branch_v_b", net.branch_v.bias)]
     else:
         out += [("warp_w", net.gaussian_warp.weight), ("warp_b", net.gaussian_warp.bias)]
-    out += [("rot_w", net.gaussian_rotation.weight), ("rot_b", net.gaussian_rotation.bias),
-            ("scale_w", net.gaussian_scaling.weight), ("scale_b", net.gaussian_scaling.bias)]
+    if hasattr(net, "gaussian_rotation"):   # (DeformNetworkODE has no rotation / scaling heads)
+        out += [("rot_w", net.gaussian_rotation.weight), ("rot_b", net.gaussian_rotation.bias),
+                ("scale_w", net.gaussian_scaling.weight), ("scale_b", net.gaussian_scaling.bias)]
     return out
 
 
@@ -204,7 +205,8 @@ class _FusedDeform(torch.autograd.Function):
 class _DeformBase(nn.Module):
     """Shared constructor: identical module tree to utils/time_utils.py:57-100 / :130-174."""
 
-    def __init__(self, D=8, W=256, input_ch=3, output_ch=59, multires=10, is_blender=False, is_6dof=False):
+    def __init__(self, D=8, W=256, input_ch=3, output_ch=59, multires=10, is_blender=False, is_6dof=False,
+                 rot_scale_heads=True):
         super().__init__()
         self.D, self.W = D, W
         self.output_ch = output_ch
@@ -231,8 +233,9 @@ class _DeformBase(nn.Module):
             self.branch_v = nn.Linear(W, 3)
         else:
             self.gaussian_warp = nn.Linear(W, 3)
-        self.gaussian_rotation = nn.Linear(W, 4)
-        self.gaussian_scaling = nn.Linear(W, 3)
+        if rot_scale_heads:
+            self.gaussian_rotation = nn.Linear(W, 4)
+            self.gaussian_scaling = nn.Linear(W, 3)
         self.debug = bool(int(os.environ.get("D3G_DEBUG", "0")))
         # opt-in: backward adds into existing .grad tensors in place (see _FusedDeform.backward); only valid
         # with loss.backward()-style accumulation, not with torch.autograd.grad()
@@ -381,6 +384,74 @@ class DeformNetwork(_DeformBase):
         return d_xyz, 0, 0
 
 
+class DeformNetworkODE(_DeformBase):
+    """utils/time_utils.py:331-438: the right-hand side dx/dt = f(t, x) of the `ode_batch*` configurations
+    (scene/deform_model.py:183-207 hands it to odeint_adjoint).  With use_linear == 0 and use_emb (every shipped
+    configuration, arguments/ode_*.py) it is the DeformNetwork trunk + gaussian_warp head, evaluated by the fused
+    kernels; gradients flow to x, t and the parameters (the adjoint needs all three).  The use_linear 1..4 variants are
+    single nn.Linear maps of the embedded input and stay torch ops, as in the reference."""
+    _heads = HEAD_WARP
+
+    def __init__(self, D=8, W=256, input_ch=3, output_ch=59, multires=10, is_blender=False, is_6dof=False,
+                 use_linear=0, use_emb=True, output_scale=1, skips=[4]):
+        if use_linear == 0:
+            if not use_emb or list(skips if skips is not None else []) != [4] or D != 8 or W != 256 or is_6dof:
+                raise NotImplementedError(
+                    "DeformNetworkODE: the fused kernels implement use_linear=0 with use_emb=True, skips=[4], D=8, "
+                    "W=256, is_6dof=False (every configuration under arguments/); got use_emb=%s skips=%s D=%d W=%d "
+                    "is_6dof=%s" % (use_emb, skips, D, W, is_6dof))
+            super().__init__(D=D, W=W, input_ch=input_ch, output_ch=output_ch, multires=multires,
+                             is_blender=is_blender, is_6dof=False, rot_scale_heads=False)
+            self.use_linear, self.use_emb, self.output_scale = use_linear, use_emb, output_scale
+            return
+        nn.Module.__init__(self)
+        self.use_linear, self.use_emb, self.output_scale = use_linear, use_emb, output_scale
+        self.D, self.W, self.input_ch, self.output_ch = D, W, input_ch, output_ch
+        self.t_multires = 6 if is_blender else 10
+        self.multires = multires
+        self.is_blender, self.is_6dof = is_blender, is_6dof
+        time_ch = 1 + 2 * self.t_multires if use_emb else 1
+        xyz_ch = 3 + 6 * multires if use_emb else 3
+        self.time_input_ch, self.xyz_input_ch, self.total_input_ch = time_ch, xyz_ch, time_ch + xyz_ch
+        if use_linear == 1:
+            self.linear_layer = nn.Linear(self.total_input_ch, 3)
+        elif use_linear == 2:
+            self.A_t_net = nn.Linear(time_ch, xyz_ch * xyz_ch)
+            self.b_t_net = nn.Linear(time_ch, xyz_ch)
+        elif use_linear == 3:
+            self.xyz_linear = nn.Linear(xyz_ch, 3)
+        elif use_linear == 4:
+            self.z_linear = nn.Linear(1, 1)
+        else:
+            raise ValueError("use_linear must be 0..4")
+
+    @staticmethod
+    def _embed(x, L):
+        out = [x]
+        for f in range(L):
+            out += [torch.sin(x * 2.0 ** f), torch.cos(x * 2.0 ** f)]
+        return torch.cat(out, -1)
+
+    def forward(self, t, x):
+        if self.use_linear == 0:
+            (d_xyz,) = self._run(x, t.reshape(1, 1) if t.numel() == 1 else t)
+            return d_xyz * self.output_scale if self.output_scale != 1 else d_xyz
+        if self.use_emb:
+            t_emb = self._embed(t.expand(x.shape[0], 1), self.t_multires)
+            x_emb = self._embed(x, self.multires)
+        else:
+            x_emb, t_emb = x, t.unsqueeze(1)
+        if self.use_linear == 1:
+            return self.linear_layer(torch.cat([x_emb, t_emb], dim=-1)) * self.output_scale
+        if self.use_linear == 2:
+            A_t = self.A_t_net(t_emb).view(-1, self.xyz_input_ch, self.xyz_input_ch)
+            return (torch.bmm(A_t, x_emb.unsqueeze(-1)).squeeze(-1) + self.b_t_net(t_emb)) * self.output_scale
+        if self.use_linear == 3:
+            return self.xyz_linear(x_emb) * self.output_scale
+        z = self.z_linear(x_emb[:, 2:3])
+        return torch.cat([torch.zeros_like(x_emb[:, :2]), z], dim=1) * self.output_scale
+
+
 def get_expon_lr_func(lr_init, lr_final, lr_delay_steps=0, lr_delay_mult=1.0, max_steps=1000000):
     """utils/general_utils.py:78-109 (log-linear interpolation with optional warm-up)."""
 
@@ -481,3 +552,48 @@ class DeformModelBaseline(_DeformModelBase):
             lr_init=training_args.position_lr_init * self.spatial_lr_scale,
             lr_final=training_args.position_lr_final, lr_delay_mult=training_args.position_lr_delay_mult,
             max_steps=training_args.deform_lr_max_steps)
+
+
+class DeformModelODE(_DeformModelBase):
+    """scene/deform_model.py:172-251: positions at the sampled times are the solution of dx/dt = deform(t, x) from
+    the canonical positions (adaptive dopri5 + adjoint).  torchdiffeq.odeint_adjoint is used when it is installed;
+    otherwise this package's own solver of the same family (ode.py)."""
+
+    def __init__(self, is_blender=False, is_6dof=False, D=8, W=256, input_ch=3, output_ch=59, multires=10,
+                 scale_lr=False, use_linear=0, use_emb=True, rtol=0.001, atol=0.0001, output_scale=1, skips=[4]):
+        self.deform = DeformNetworkODE(is_blender=is_blender, is_6dof=is_6dof, D=D, W=W, input_ch=input_ch,
+                                       output_ch=output_ch, multires=multires, use_linear=use_linear, use_emb=use_emb,
+                                       output_scale=output_scale, skips=skips).cuda()
+        self.optimizer = None
+        self.spatial_lr_scale = 5
+        self.scale_lr = scale_lr
+        self.rtol, self.atol = rtol, atol
+
+    def step(self, xyz, time_emb):
+        is_val = len(time_emb) == 1
+        if is_val and float(time_emb[0]) == 0.0:
+            return xyz, torch.zeros([xyz.shape[0], 4]).to(xyz.device), torch.zeros([xyz.shape[0], 3]).to(xyz.device)
+        t_interval = torch.Tensor(time_emb).to(xyz.device)
+        try:
+            from torchdiffeq import odeint_adjoint
+        except ImportError:
+            from .ode import odeint_adjoint
+        ode_value = odeint_adjoint(self.deform, xyz, t_interval, rtol=self.rtol, atol=self.atol)
+        xyz_new = torch.squeeze(ode_value)
+        rotation = torch.zeros([xyz_new.shape[0], xyz_new.shape[1], 4]).to(xyz.device)
+        scale = torch.zeros([xyz_new.shape[0], xyz_new.shape[1], 3]).to(xyz.device)
+        return xyz_new, rotation, scale
+
+    def train_setting(self, training_args):
+        l = [{"params": list(self.deform.parameters()),
+              "lr": training_args.position_lr_init * self.spatial_lr_scale, "name": "deform"}]
+        self.optimizer = _FusedAdam(l, lr=0.0, eps=1e-15, weight_decay=training_args.weight_decay)
+        if self.scale_lr:
+            lr_init = training_args.position_lr_init * self.spatial_lr_scale * training_args.num_cams_per_iter
+            lr_final = training_args.position_lr_final * self.spatial_lr_scale * training_args.num_cams_per_iter
+        else:
+            lr_init = training_args.position_lr_init * self.spatial_lr_scale
+            lr_final = training_args.position_lr_final
+        self.deform_scheduler_args = get_expon_lr_func(lr_init=lr_init, lr_final=lr_final,
+                                                       lr_delay_mult=training_args.position_lr_delay_mult,
+                                                       max_steps=training_args.position_lr_max_steps)
