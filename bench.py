@@ -1,16 +1,23 @@
 #!/usr/bin/env python
 """bench.py — deform+raster fwd+bwd frames/sec (BASELINE.json metric) on 1..8 B200.
 
-One "step" = one (camera, timestamp) frame per GPU through the reference-facing API of this repo:
+One "step" = one batch of (camera, timestamp) frames through the reference-facing API of this repo:
     d_xyz, d_rot, d_scale = DeformModelBaseline.step(xyz.detach(), fid.expand(N,1))   # fused tcgen05 MLP
     out = render(cam, gaussians, pipe, bg, d_xyz, d_rot, d_scale)                     # CUDA rasterizer
-    loss = 0.8*l1(out["render"], gt) + 0.2*(1-ssim(out["render"], gt)); loss.backward()                                     # raster bwd + MLP bwd
+    loss = 0.8*l1(out["render"], gt) + 0.2*(1-ssim(out["render"], gt)); loss.backward()   # raster bwd + MLP bwd
 (scene/deform_model.py:323-324, gaussian_renderer/__init__.py:32-133, train_baseline.py:109-128).
-With N > 1 every rank renders its own frame of the camera/time batch and the Gaussian-parameter and MLP
-gradients are summed with one NCCL all-reduce over a flat buffer (weak scaling: one frame per GPU per step).
 
-Workload = BASELINE.json configs[1] ("C2"): 100k Gaussians, SH degree 3, 800x800, synthetic scene of
-SURVEY.md §8(d).  `--impl reference` times the CPU restatement (oracle/) on the host cores.
+Configurations (BASELINE.json `configs`, --config):
+  C2 (default, the headline): 100k Gaussians, SH degree 3, 800x800, ONE frame per GPU per step (weak scaling);
+     with N > 1 GPUs every rank renders its own frame and the Gaussian + MLP gradients are summed with one NCCL
+     all-reduce of a flat buffer.
+  C1 / C4: 50k @400x400, 200k 6-DoF @800x800, same step.
+  C3: 300k Gaussians, a 10-frame camera/time batch per step (the per-iteration loop of train.py:148-154,224-250 with its
+     cumulative-L1 loss weights), frames k = rank, rank+G, ... on each of G GPUs, all of a rank's timestamps in ONE MLP
+     launch, one all-reduce per step (strong scaling over the batch; bounded by ceil(10/G) frames on the busiest rank).
+  C5: render-only, 1M Gaussians @1920x1080, 100-timestamp sweep with a fixed camera under no_grad
+     (render_baseline.py:57-74, render.py:186-202), timestamps k = rank mod G, no collective.
+`--impl reference` times the reference's CPU implementation of the same path on the host cores (see CpuArm).
 """
 import argparse
 import importlib
@@ -29,12 +36,15 @@ if ROOT not in sys.path:
 PKG = "deformable-3d-gaussians_b200"
 
 CONFIGS = {
-    # name: (N gaussians, H, W, is_6dof, scene kind)
-    "C1": dict(N=50000, H=400, W=400, is_6dof=False, kind="blob"),
-    "C2": dict(N=100000, H=800, W=800, is_6dof=False, kind="uniform"),
-    "C4": dict(N=200000, H=800, W=800, is_6dof=True, kind="uniform"),
+    # frames: frames per step (None = one per GPU, weak scaling); train: fwd+bwd + gradient exchange
+    "C1": dict(N=50000, H=400, W=400, is_6dof=False, kind="blob", frames=None, train=True),
+    "C2": dict(N=100000, H=800, W=800, is_6dof=False, kind="uniform", frames=None, train=True),
+    "C3": dict(N=300000, H=800, W=800, is_6dof=False, kind="uniform", frames=10, train=True),
+    "C4": dict(N=200000, H=800, W=800, is_6dof=True, kind="uniform", frames=None, train=True),
+    "C5": dict(N=1000000, H=1080, W=1920, is_6dof=False, kind="uniform", frames=100, train=False),
 }
 METRIC = "deform+raster fwd+bwd frames/sec @100k Gaussians 800x800, 1/2/4/8 B200"
+LAMBDA_DSSIM = 0.2   # arguments/__init__.py:119
 
 
 def pkg(sub):
@@ -44,13 +54,19 @@ def pkg(sub):
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=None)
+    ap.add_argument("--warmup", type=int, default=None)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="C2", choices=sorted(CONFIGS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
-    return ap.parse_args()
+    a = ap.parse_args()
+    single = CONFIGS[a.config]["frames"] is None
+    if a.steps is None:
+        a.steps = 200 if single else (10 if a.config == "C3" else 3)   # 20 warm-up + 200 timed
+    if a.warmup is None:
+        a.warmup = 20 if single else 3
+    return a
 
 
 def peaks():
@@ -97,138 +113,203 @@ class ClockSampler(threading.Thread):
                 "samples": len(s)}
 
 
+def frame_schedule(cfg, world):
+    """(theta_deg, fid) of every frame of one step, in time order."""
+    T = cfg["frames"] if cfg["frames"] is not None else world
+    if not cfg["train"]:   # C5: fixed camera, t = i/(T-1) (render.py:186-202)
+        return [(20.0, k / (T - 1)) for k in range(T)]
+    if T == 1:
+        return [(20.0, 0.37)]
+    return [(-180.0 + 360.0 * (k + 0.5) / T, k / (T - 1)) for k in range(T)]
+
+
+def scaled_network(deform, cfg, device=None):
+    """DeformNetworkBaseline(is_blender=True) with torch's seeded default init, heads scaled so the splats stay sane
+    (SURVEY.md 8(d)); both bench arms use exactly these parameters."""
+    import torch
+    torch.manual_seed(0)
+    model = deform.DeformModelBaseline(is_blender=True, is_6dof=cfg["is_6dof"])
+    with torch.no_grad():
+        net = model.deform
+        for m in (net.gaussian_rotation, net.gaussian_scaling):
+            m.weight.mul_(0.01); m.bias.mul_(0.01)
+        if cfg["is_6dof"]:
+            for m in (net.branch_w, net.branch_v):
+                m.weight.mul_(0.01); m.bias.mul_(0.01)
+        else:
+            net.gaussian_warp.weight.mul_(0.1); net.gaussian_warp.bias.mul_(0.1)
+    return model
+
+
 # ------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------
 class Workload:
-    """Scene, network and one frame of inputs on `device`; host copies of the per-frame inputs pinned."""
+    """Scene, network and this rank's frames of one step on `device`; host copies of the per-frame inputs pinned."""
 
-    def __init__(self, cfg, rank, device):
+    def __init__(self, cfg, rank, world, device):
         import torch
-        synth, deform = pkg("synth"), pkg("deform")
+        synth, deform, frames = pkg("synth"), pkg("deform"), pkg("frames")
         self.torch = torch
-        self.cfg, self.device = cfg, device
+        self.cfg, self.device, self.world = cfg, device, world
         N, H, W = cfg["N"], cfg["H"], cfg["W"]
         g = synth.SynthGaussians(N, seed=0, kind=cfg["kind"], sh_degree=3, device="cpu")
         for name in ("_xyz", "_features_dc", "_features_rest", "_opacity", "_scaling", "_rotation"):
-            setattr(g, name, getattr(g, name).to(device).requires_grad_(True))
+            setattr(g, name, getattr(g, name).to(device).requires_grad_(cfg["train"]))
         self.gaussians = g
-        torch.manual_seed(0)
-        self.model = deform.DeformModelBaseline(is_blender=True, is_6dof=cfg["is_6dof"])
-        with torch.no_grad():  # keep the deformation small so the splats stay sane (SURVEY.md §8(d))
-            net = self.model.deform
-            for m in (net.gaussian_rotation, net.gaussian_scaling):
-                m.weight.mul_(0.01); m.bias.mul_(0.01)
-            if cfg["is_6dof"]:
-                for m in (net.branch_w, net.branch_v):
-                    m.weight.mul_(0.01); m.bias.mul_(0.01)
-            else:
-                net.gaussian_warp.weight.mul_(0.1); net.gaussian_warp.bias.mul_(0.1)
-        # frame of this rank: camera on the D-NeRF orbit, timestamp in [0,1]
-        world = int(os.environ.get("WORLD_SIZE", "1"))
-        theta = -180.0 + 360.0 * (rank + 0.5) / max(world, 1) if world > 1 else 20.0
-        fid = (rank / (world - 1)) if world > 1 else 0.37
-        cam = synth.make_camera(W, H, theta_deg=theta, fid=fid)
-        self.cam_host = cam
-        gt = torch.rand(3, H, W, generator=torch.Generator().manual_seed(100 + rank))
-        self.host = dict(view=cam.world_view_transform.pin_memory(), proj=cam.full_proj_transform.pin_memory(),
-                         campos=cam.camera_center.pin_memory(), fid=cam.fid.pin_memory(), gt=gt.pin_memory())
-        self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.host.values())
-        self.dev = {k: v.to(device) for k, v in self.host.items()}
-        self.cam = synth.camera_to(cam, device)
+        self.model = scaled_network(deform, cfg)
+        sched = frame_schedule(cfg, world)
+        self.frames_per_step = len(sched)
+        self.mine = frames.shard_frames(len(sched), world, rank)
+        self.frames_per_rank = [len(frames.shard_frames(len(sched), world, r)) for r in range(world)]
+        weights = frames.frame_loss_weights(len(sched), LAMBDA_DSSIM) if cfg["frames"] else [(1.0 - LAMBDA_DSSIM, LAMBDA_DSSIM)]
+        self.cams_host, self.cams, self.host, self.dev, self.weights = [], [], [], [], []
+        for j, k in enumerate(self.mine):
+            theta, fid = sched[k]
+            cam = synth.make_camera(W, H, theta_deg=theta, fid=fid)
+            self.cams_host.append(cam)
+            h = dict(view=cam.world_view_transform.pin_memory(), proj=cam.full_proj_transform.pin_memory(),
+                     campos=cam.camera_center.pin_memory(), fid=cam.fid.pin_memory())
+            if cfg["train"]:
+                h["gt"] = torch.rand(3, H, W, generator=torch.Generator().manual_seed(100 + k)).pin_memory()
+            self.host.append(h)
+            self.dev.append({kk: v.to(device) for kk, v in h.items()})
+            self.cams.append(synth.camera_to(cam, device))
+            self.weights.append(weights[k if cfg["frames"] else 0])
+        self.h2d_bytes = sum(t.numel() * t.element_size() for h in self.host for t in h.values())
+        self.fids_dev = torch.zeros(max(len(self.mine), 1), device=device)
         self.bg = torch.zeros(3, device=device)
         self.pipe = type("Pipe", (), dict(convert_SHs_python=False, compute_cov3D_python=False, debug=False))()
-        # flat gradient buffer: parameter .grad tensors are views into it, so the multi-GPU exchange is
-        # one all-reduce with no packing kernel
-        # D3G_BENCH_EARLY=1: all-reduce the Gaussian slice from inside backward, overlapping the MLP backward.  Measured
-        # at 4 GPUs it does not pay (the persistent MLP kernels own every SM, the NCCL CTAs only delay them): 1.62k vs
-        # 1.70k frames/s end to end, so the default is one all-reduce after backward
-        self.grads = pkg("frames").FlatGrads(g.parameters() + list(self.model.deform.parameters()),
-                                             early=len(g.parameters()) if (world > 1 and os.environ.get("D3G_BENCH_EARLY", "0") == "1") else 0)
-        self.flat = self.grads.flat
-        # MLP backward adds straight into those .grad views (no per-parameter zero-fill + AccumulateGrad add)
-        self.model.deform.fused_grad_accumulation = True
-        # sync-free frames: the binning workspace is sized from the largest pair count seen so far (+10 %) instead of
-        # reading `num_rendered` back in the middle of every frame; overflow is checked where the host syncs anyway
-        self.training_loss = pkg("loss_utils").training_loss
+        if cfg["train"]:
+            # flat gradient buffer: parameter .grad tensors are views into it, so the multi-GPU exchange is
+            # one all-reduce with no packing kernel
+            self.grads = frames.FlatGrads(g.parameters() + list(self.model.deform.parameters()),
+                                          early=len(g.parameters()) if (world > 1 and os.environ.get("D3G_BENCH_EARLY", "0") == "1") else 0)
+            self.grads.frames_per_reduce = max(len(self.mine), 1)
+            self.flat = self.grads.flat
+            # MLP backward adds straight into those .grad views (no per-parameter zero-fill + AccumulateGrad add)
+            self.model.deform.fused_grad_accumulation = True
+        else:
+            self.grads = self.flat = None
+        # sync-free frames: the binning workspace is sized from the largest pair count seen so far (+ headroom) instead
+        # of reading `num_rendered` back in the middle of every frame; overflow is checked where the host syncs anyway
         ras = pkg("rasterizer")
-        self.capacity = ras.GrowingPairCapacity(1.1)
+        self.capacity = ras.GrowingPairCapacity(1.1 if len(sched) == world else 1.5)
         ras.PAIR_CAPACITY_POLICY = self.capacity
+        self.image_loss = pkg("loss_utils")._ImageLoss
         self.loss_host = torch.zeros(8).pin_memory()
-        self.frames_done = 0
+        self.steps_done = 0
         self.losses = []
         self.copy_stream = torch.cuda.Stream(device=device)
         self.gt_ready = torch.cuda.Event()
         self.last = None
 
-    def frame(self, from_host):
-        """One fwd+bwd frame.  from_host: copy this frame's inputs from pinned host memory first and read
-        the loss back (the end-to-end leg); otherwise everything is already resident."""
+    def _upload(self):
+        torch = self.torch
+        for cam, h, d in zip(self.cams, self.host, self.dev):
+            cam.world_view_transform.copy_(h["view"], non_blocking=True)
+            cam.full_proj_transform.copy_(h["proj"], non_blocking=True)
+            cam.camera_center.copy_(h["campos"], non_blocking=True)
+            cam.fid.copy_(h["fid"], non_blocking=True)
+        if self.cfg["train"]:
+            # the ground-truth images are only needed by the loss: upload them on a copy stream so the PCIe transfer
+            # overlaps the deformation MLP and the rasterizer of the same step
+            main = torch.cuda.current_stream()
+            self.copy_stream.wait_stream(main)  # last step's loss has finished reading the buffers
+            with torch.cuda.stream(self.copy_stream):
+                for h, d in zip(self.host, self.dev):
+                    d["gt"].copy_(h["gt"], non_blocking=True)
+                self.gt_ready.record(self.copy_stream)
+
+    def step(self, from_host):
+        """One step = this rank's frames, fwd (+bwd).  from_host: copy the step's inputs from pinned host memory first
+        and read the result back (the end-to-end leg); otherwise everything is already resident."""
         torch = self.torch
         render = pkg("renderer").render
-        cam, g = self.cam, self.gaussians
+        g, cfg = self.gaussians, self.cfg
         if from_host:
-            cam.world_view_transform.copy_(self.host["view"], non_blocking=True)
-            cam.full_proj_transform.copy_(self.host["proj"], non_blocking=True)
-            cam.camera_center.copy_(self.host["campos"], non_blocking=True)
-            cam.fid.copy_(self.host["fid"], non_blocking=True)
-            # the ground-truth image (7.7 MB) is only needed by the loss: upload it on a copy stream so the
-            # PCIe transfer overlaps the deformation MLP and the rasterizer of the same frame
-            main = torch.cuda.current_stream()
-            self.copy_stream.wait_stream(main)  # last frame's loss has finished reading the buffer
-            with torch.cuda.stream(self.copy_stream):
-                self.dev["gt"].copy_(self.host["gt"], non_blocking=True)
-                self.gt_ready.record(self.copy_stream)
-        self.flat.zero_()
+            self._upload()
+        if not self.mine:
+            return None
         N = g.get_xyz.shape[0]
-        time_input = cam.fid.unsqueeze(0).expand(N, -1)
-        d_xyz, d_rot, d_scale = self.model.step(g.get_xyz.detach(), time_input)
-        out = render(cam, g, self.pipe, self.bg, d_xyz, d_rot, d_scale, self.cfg["is_6dof"])
+        T = len(self.mine)
+        if cfg["train"]:
+            self.flat.zero_()
+            if T == 1:   # the reference's single-frame call (train_baseline.py:109-115)
+                time_input = self.cams[0].fid.unsqueeze(0).expand(N, -1)
+                d_xyz, d_rot, d_scale = self.model.step(g.get_xyz.detach(), time_input)
+                d_xyz, d_rot, d_scale = [d_xyz], [d_rot], [d_scale]
+            else:        # every timestamp of this rank's share of the batch in ONE launch
+                for j, cam in enumerate(self.cams):
+                    self.fids_dev[j:j + 1].copy_(cam.fid, non_blocking=True)
+                d_xyz, d_rot, d_scale = self.model.deform.forward_times(g.get_xyz.detach(), self.fids_dev[:T])
+            if from_host:
+                torch.cuda.current_stream().wait_event(self.gt_ready)
+            loss = None
+            for j, cam in enumerate(self.cams):
+                out = render(cam, g, self.pipe, self.bg, d_xyz[j], d_rot[j], d_scale[j], cfg["is_6dof"])
+                wl1, wss = self.weights[j]
+                lj = self.image_loss.apply(out["render"], self.dev[j]["gt"], wl1, -wss, wss)  # train.py:245-250
+                loss = lj if loss is None else loss + lj
+            loss.backward()
+            self.last = out
+            result = loss.detach()
+        else:
+            with torch.no_grad():
+                result = torch.zeros((), device=self.device)
+                CH = 4   # timestamps per MLP launch
+                for c0 in range(0, T, CH):
+                    idx = list(range(c0, min(T, c0 + CH)))
+                    for j in idx:
+                        self.fids_dev[j:j + 1].copy_(self.cams[j].fid, non_blocking=True)
+                    d_xyz, d_rot, d_scale = self.model.deform.forward_times(g.get_xyz, self.fids_dev[c0:c0 + len(idx)])
+                    for i, j in enumerate(idx):
+                        out = render(self.cams[j], g, self.pipe, self.bg, d_xyz[i], d_rot[i], d_scale[i], False)
+                        result = result + out["render"][:, ::64, ::64].sum()   # a checksum that depends on every frame
+                self.last = out
         if from_host:
-            torch.cuda.current_stream().wait_event(self.gt_ready)
-        loss = self.training_loss(out["render"], self.dev["gt"], 0.2)   # train_baseline.py:126-127, fused
-        loss.backward()
-        self.last = out
-        if from_host:
-            # the loss travels to pinned host memory every frame; the host reads it when it next waits for this
-            # frame (timed_region keeps at most two frames in flight), like a training loop that logs one step late
-            slot = self.frames_done % self.loss_host.numel()
-            self.loss_host[slot:slot + 1].copy_(loss.detach().reshape(1), non_blocking=True)
-            self.frames_done += 1
+            # the result travels to pinned host memory every step; the host reads it when it next waits for this
+            # step (timed_region keeps at most two steps in flight), like a training loop that logs one step late
+            slot = self.steps_done % self.loss_host.numel()
+            self.loss_host[slot:slot + 1].copy_(result.reshape(1), non_blocking=True)
+            self.steps_done += 1
             return slot
         return None
 
+    def exchange(self):
+        if self.world > 1 and self.cfg["train"]:
+            self.grads.all_reduce()
+
 
 def timed_region(work, steps, from_host, world, dist):
-    """barrier + sync, K frames, sync + barrier; returns max-over-ranks seconds (CUDA events)."""
+    """barrier + sync, K steps, sync + barrier; returns (max-over-ranks seconds, per-step ms list of this rank)."""
     torch = work.torch
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    # the host may run at most `depth` frames ahead of the device (launch latency stays hidden, the queues of
+    # the host may run at most `depth` steps ahead of the device (launch latency stays hidden, the queues of
     # several ranks cannot drift arbitrarily far apart); 0 = unbounded
     depth = int(os.environ.get("D3G_BENCH_INFLIGHT", "2"))
-    marks = []
+    marks, stamps = [], [e0]
 
     def retire(block_all=False):
         while marks and (block_all or len(marks) >= max(depth, 1)):
             ev, slot = marks.pop(0)
             ev.synchronize()
-            if slot is not None:   # end-to-end leg: consume the frame's loss on the host, verify its pair capacity
+            if slot is not None:   # end-to-end leg: consume the step's result on the host, verify its pair capacity
                 work.losses.append(float(work.loss_host[slot]))
                 work.capacity.check()
 
     for _ in range(steps):
         retire()
-        slot = work.frame(from_host)
-        if world > 1:
-            work.grads.all_reduce()
-        if depth or from_host:
-            ev = torch.cuda.Event()
-            ev.record()
-            marks.append((ev, slot))
+        slot = work.step(from_host)
+        work.exchange()
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        stamps.append(ev)
+        marks.append((ev, slot))
         if not depth:
             retire(block_all=from_host)
     retire(block_all=True)
@@ -236,17 +317,18 @@ def timed_region(work, steps, from_host, world, dist):
     torch.cuda.synchronize()
     work.capacity.check()
     sec = e0.elapsed_time(e1) / 1e3
+    per_step = [stamps[i].elapsed_time(stamps[i + 1]) for i in range(len(stamps) - 1)]
     if world > 1:
         t = torch.tensor([sec], device=work.device)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         sec = float(t.item())
         dist.barrier()
-    return sec
+    return sec, per_step
 
 
 def kernel_table(work, steps):
     """Second pass with the library's per-kernel CUDA-event recorder on (events on the launching stream);
-    returns {kernel: (avg ms per launch, launches per step)} and the pair count R of the frame."""
+    returns {kernel: (avg ms per launch, launches per step)} and the mean pair count R of a frame."""
     import ctypes as C
     torch = work.torch
     lib = pkg("_lib").load()
@@ -254,8 +336,8 @@ def kernel_table(work, steps):
     torch.cuda.synchronize()
     lib.d3g_prof_enable(1)
     for _ in range(steps):
-        work.frame(False)
-        work.grads.all_reduce()  # no-op on one rank
+        work.step(False)
+        work.exchange()
     ms = (C.c_double * n)()
     cnt = (C.c_int32 * n)()
     pkg("_lib").check(lib.d3g_prof_collect(ms, cnt, n))
@@ -279,8 +361,8 @@ def ncu_traffic(config_name):
         return json.load(f).get("kernels", {})
 
 
-def roofline(table, R, cfg, pk, traffic=None):
-    """Algorithmic bytes / flops per launch over measured duration."""
+def roofline(table, R, cfg, pk, rows_per_mlp_launch, traffic=None):
+    """Algorithmic bytes / flops per launch (DESIGN.md kernels table) over measured duration."""
     traffic = traffic or {}
     N, P = cfg["N"], cfg["H"] * cfg["W"]
     Tl = ((cfg["W"] + 15) // 16) * ((cfg["H"] + 15) // 16)
@@ -288,12 +370,15 @@ def roofline(table, R, cfg, pk, traffic=None):
     # bytes each rasterizer stage must move once (inputs read once, outputs written once)
     algo_bytes = {
         "preprocess_fwd": 311 * N, "scan": 8 * N, "duplicate_with_keys": 20 * N + 12 * R, "radix_sort": 24 * R,
-        "identify_tile_ranges": 8 * R + 8 * Tl, "render_fwd": 44 * R + 24 * P, "render_bwd": 88 * R + 32 * P,
-        "preprocess_bwd": 600 * N,
+        "tile_sort": 24 * R, "identify_tile_ranges": 8 * R + 8 * Tl, "render_fwd": 44 * R + 24 * P,
+        "render_bwd": 88 * R + 32 * P, "preprocess_bwd": 600 * N,
     }
-    # flops per point (519,936 MAC forward incl. heads; backward = dgrad chain 7*65536+16*256 MAC, wgrad = forward MACs)
-    mlp_flops = {"mlp_fwd": 2 * 519936 * N, "mlp_dgrad": 2 * (7 * 65536 + 4096) * N,
-                 "mlp_wgrad": 2 * (7 * 65536 + 2 * 96 * 256 + 16 * 256) * N}
+    # ALGORITHMIC flops per point (519,936 MAC forward incl. heads; dgrad chain 7*65536+16*256 MAC, wgrad = forward
+    # MACs).  The kernels ISSUE more tensor work than that: three split-fp16 products in the forward, two in the dgrad
+    # chain (kind::f16 at the bf16 rate, so the bf16 peak is the denominator); `issued` says how much.
+    M = rows_per_mlp_launch
+    mlp_flops = {"mlp_fwd": (2 * 519936 * M, 3.0), "mlp_dgrad": (2 * (7 * 65536 + 4096) * M, 2.0),
+                 "mlp_wgrad": (2 * (7 * 65536 + 2 * 96 * 256 + 16 * 256) * M, 1.0)}
     rows = []
     for name, (ms, per_step) in table.items():
         if name in algo_bytes:
@@ -301,10 +386,11 @@ def roofline(table, R, cfg, pk, traffic=None):
             rows.append(dict(kernel=name, bound="hbm", achieved=ach, peak=pk["hbm_gbs"], unit="GB/s",
                              frac=ach / pk["hbm_gbs"], ms=ms, launches_per_step=per_step))
         elif name in mlp_flops:
-            ach = mlp_flops[name] / (ms * 1e-3) / 1e12
-            # tf32 runs at half the bf16 rate; the measured bf16 figure is the denominator the recipe names
+            fl, mult = mlp_flops[name]
+            ach = fl / (ms * 1e-3) / 1e12
             rows.append(dict(kernel=name, bound="tensor", achieved=ach, peak=pk["bf16_tflops_sustained"], unit="TFLOP/s",
-                             frac=ach / pk["bf16_tflops_sustained"], ms=ms, launches_per_step=per_step))
+                             frac=ach / pk["bf16_tflops_sustained"], issued=ach * mult,
+                             issued_frac=ach * mult / pk["bf16_tflops_sustained"], ms=ms, launches_per_step=per_step))
         else:
             rows.append(dict(kernel=name, bound=None, ms=ms, launches_per_step=per_step))
     for r in rows:
@@ -314,86 +400,190 @@ def roofline(table, R, cfg, pk, traffic=None):
 
 
 # ------------------------------------------------------------------------------------------------
-# CPU arm: the oracle (CPU restatement of the path) on the host cores, on a bounded sample
+# reference arm: the reference's CPU implementation of the path on the host cores
 # ------------------------------------------------------------------------------------------------
 class CpuArm:
-    """Sample = the first 1/FRACTION of the config's Gaussians (scales unchanged) through the numpy MLP
-    oracle fwd+bwd and the C/OpenMP rasterizer oracle fwd+bwd at the full resolution; the frame time is
-    scaled by FRACTION (both stages are linear in the number of Gaussians / pairs)."""
-    FRACTION = 10
+    """One FULL frame of the configuration per step, nothing scaled:
+      * deformation MLP: the reference's DeformNetworkBaseline.forward (utils/time_utils.py:102-127) as it runs —
+        torch ops (nn.Linear, ReLU, cat, sin/cos), forward + autograd backward, torch.set_num_threads(all host cores).
+        /root/reference does not exist on the GPU box, so the module is restated op by op (kind "port"); it carries
+        the SAME parameters as the GPU arm (one state_dict).
+      * rasterizer: the reference has no CPU rasterizer (its CUDA extension's source is absent from the archive); the
+        C restatement under oracle/ (OpenMP over tiles) stands in, forward + backward, labelled "port".
+      * loss: 0.8 L1 + 0.2 (1 - SSIM) of the reference's utils/loss_utils.py restated in numpy (oracle/loss_ref.py).
+    """
 
     def __init__(self, cfg):
         import torch
-        from oracle import mlp_ref, raster_oracle as ro
-        synth = pkg("synth")
-        self.ro, self.cfgd = ro, cfg
+        from oracle import raster_oracle as ro, loss_ref
+        synth, deform = pkg("synth"), pkg("deform")
+        self.torch, self.ro, self.loss_ref, self.cfgd = torch, ro, loss_ref, cfg
         N, H, W = cfg["N"], cfg["H"], cfg["W"]
-        n = N // self.FRACTION
+        self.cores = os.cpu_count() or 1
+        torch.set_num_threads(self.cores)
         g = synth.SynthGaussians(N, seed=0, kind=cfg["kind"], sh_degree=3)
-        cam = synth.make_camera(W, H, theta_deg=20.0, fid=0.37)
-        self.n = n
-        self.xyz = g.get_xyz[:n].numpy()
-        self.feat = g.get_features[:n].numpy()
-        self.opac = g.get_opacity[:n].numpy()
-        self.scal = g.get_scaling[:n].numpy()
-        self.rot = g.get_rotation[:n].numpy()
+        theta, fid = frame_schedule(cfg, 1)[0]
+        cam = synth.make_camera(W, H, theta_deg=theta, fid=fid)
+        self.g, self.fid = g, float(fid)
         self.rcfg = ro.make_cfg(H, W, math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5), np.zeros(3), 1.0,
                                 cam.world_view_transform.numpy(), cam.full_proj_transform.numpy(),
                                 cam.camera_center.numpy(), 3, 16, 2, np.float32)
-        params = mlp_ref.seeded_params(0, True, cfg["is_6dof"], head_scale=0.01)
-        self.mlp = mlp_ref.DeformRef(params, True, cfg["is_6dof"], True, dtype=np.float32)
-        self.dimg = (np.sign(np.random.default_rng(0).standard_normal((3, H, W))) / (3 * H * W)).astype(np.float32)
-        self.t = np.array([[0.37]], np.float32)
-        self.cores = os.cpu_count() or 1
-        torch.set_num_threads(self.cores)
+        sd = {k: v.detach().cpu() for k, v in scaled_network(deform_cpu_shim(), cfg).deform.state_dict().items()}
+        self.net = TorchDeform(cfg["is_6dof"])
+        self.net.load_state_dict(sd)
+        self.gt = torch.rand(3, H, W, generator=torch.Generator().manual_seed(100)).numpy()
 
     def frame(self):
-        d_xyz, d_rot, d_scale = self.mlp.forward(self.xyz, self.t)
-        if self.cfgd["is_6dof"]:
-            hom = np.concatenate([self.xyz, np.ones((self.n, 1), np.float32)], 1)
-            m = np.einsum("nij,nj->ni", d_xyz, hom)
-            means = m[:, :3] / m[:, 3:]
+        torch, cfg, g = self.torch, self.cfgd, self.g
+        N = g.get_xyz.shape[0]
+        xyz = g.get_xyz
+        t = torch.full((1, 1), self.fid).expand(N, 1)
+        d_xyz, d_rot, d_scale = self.net(xyz, t)
+        with torch.no_grad():
+            if cfg["is_6dof"]:
+                hom = torch.cat([xyz, torch.ones(N, 1)], 1)
+                m = torch.einsum("nij,nj->ni", d_xyz, hom)
+                means = m[:, :3] / m[:, 3:]
+            else:
+                means = xyz + d_xyz
+            scales = g.get_scaling + d_scale
+            rots = g.get_rotation + d_rot
+        ro = self.ro
+        fwd = ro.forward(self.rcfg, means.numpy(), g.get_features.numpy(), None, g.get_opacity.numpy(), scales.numpy(),
+                         rots.numpy(), None, np.float32)
+        dimg = self.loss_ref.training_loss_grad(fwd["color"].astype(np.float32), self.gt, LAMBDA_DSSIM).astype(np.float32)
+        gb = ro.backward(self.rcfg, fwd, dimg, None, np.float32)
+        R = fwd["R"]
+        gr = dict(means3D=gb["dL_dmeans3D"], rots=gb["dL_drots"], scales=gb["dL_dscales"])
+        if cfg["is_6dof"]:
+            gd = torch.zeros(N, 4, 4)   # (chain through from_homogenous omitted: same MLP backward cost)
+            gd[:, :3, 3] = torch.from_numpy(gr["means3D"])
         else:
-            means = self.xyz + 0.1 * d_xyz
-        R, color, depth, gr = self.ro.frame_fwd_bwd_f32(self.rcfg, means, self.feat, self.opac, self.scal + d_scale,
-                                                       self.rot + d_rot, self.dimg)
-        g_dxyz = gr["means3D"] if not self.cfgd["is_6dof"] else np.zeros((self.n, 4, 4), np.float32)
-        self.mlp.backward(g_dxyz, gr["rots"], gr["scales"])
+            gd = torch.from_numpy(gr["means3D"])
+        torch.autograd.backward([d_xyz, d_rot, d_scale], [gd, torch.from_numpy(gr["rots"]), torch.from_numpy(gr["scales"])])
+        for p in self.net.parameters():
+            p.grad = None
         return R
 
-    def time(self, steps, warmup):
-        for _ in range(warmup):
+    def time(self, steps, warmup, budget_s=None):
+        """Returns (seconds per frame, steps actually timed, warm-up frames actually run)."""
+        t0 = time.perf_counter()
+        for _ in range(max(warmup, 1) if budget_s is None else 1):
             self.frame()
+        w = max(warmup, 1) if budget_s is None else 1
+        first = time.perf_counter() - t0
+        if budget_s is not None:
+            steps = max(1, min(steps, int((budget_s - first) / max(first / w, 1e-6))))
         t0 = time.perf_counter()
         for _ in range(steps):
             self.frame()
-        sec = (time.perf_counter() - t0) / steps
-        return sec * self.FRACTION  # seconds per full frame
+        return (time.perf_counter() - t0) / steps, steps, w
 
-    def sample_text(self):
-        return ("first %d of %d Gaussians (1/%d), full %dx%d image, numpy MLP oracle + C/OpenMP rasterizer oracle "
-                "fwd+bwd, frame time scaled x%d" % (self.n, self.cfgd["N"], self.FRACTION, self.cfgd["H"],
-                                                    self.cfgd["W"], self.FRACTION))
+    def sample_text(self, steps):
+        c = self.cfgd
+        return ("%d full frame(s) of the configuration (%d Gaussians, %dx%d, nothing scaled): torch-CPU "
+                "DeformNetworkBaseline fwd+bwd restated op by op from utils/time_utils.py:102-127 with the GPU arm's "
+                "parameters + C/OpenMP rasterizer restatement fwd+bwd + numpy L1/SSIM loss" % (steps, c["N"], c["W"], c["H"]))
+
+
+def deform_cpu_shim():
+    """scaled_network() only needs a `DeformModelBaseline(is_blender, is_6dof)` factory whose `.deform` has the
+    reference's parameter names; on the reference arm no CUDA library may be touched, so this builds the module tree of
+    the product's DeformNetworkBaseline on the CPU without loading libd3g.so."""
+    deform = pkg("deform")
+
+    class _M:
+        def __init__(self, is_blender=False, is_6dof=False):
+            self.deform = deform.DeformNetworkBaseline(is_blender=is_blender, is_6dof=is_6dof)
+
+    return type("shim", (), {"DeformModelBaseline": _M})
+
+
+def TorchDeform(is_6dof):
+    import torch
+    import torch.nn as nn
+
+    def embed(x, L):
+        out = [x]
+        for f in range(L):
+            out += [torch.sin(x * 2.0 ** f), torch.cos(x * 2.0 ** f)]
+        return torch.cat(out, -1)
+
+    class Net(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.timenet = nn.Sequential(nn.Linear(13, 256), nn.ReLU(inplace=True), nn.Linear(256, 30))
+            self.linear = nn.ModuleList([nn.Linear(93, 256)] + [nn.Linear(256, 256) if i != 4 else nn.Linear(349, 256)
+                                                                 for i in range(7)])
+            if is_6dof:
+                self.branch_w, self.branch_v = nn.Linear(256, 3), nn.Linear(256, 3)
+            else:
+                self.gaussian_warp = nn.Linear(256, 3)
+            self.gaussian_rotation, self.gaussian_scaling = nn.Linear(256, 4), nn.Linear(256, 3)
+
+        def forward(self, x, t):
+            te = self.timenet(embed(t, 6))
+            xe = embed(x, 10)
+            h = torch.cat([xe, te], -1)
+            for i, l in enumerate(self.linear):
+                h = torch.relu(l(h))
+                if i == 4:
+                    h = torch.cat([xe, te, h], -1)
+            if is_6dof:   # utils/time_utils.py:114-121 + utils/rigid_utils.py:60-83
+                w, v = self.branch_w(h), self.branch_v(h)
+                theta = torch.norm(w, dim=-1, keepdim=True)
+                w, v = w / theta + 1e-5, v / theta + 1e-5
+                W = torch.zeros(w.shape[0], 3, 3)
+                W[:, 0, 1], W[:, 0, 2], W[:, 1, 0] = -w[:, 2], w[:, 1], w[:, 2]
+                W[:, 1, 2], W[:, 2, 0], W[:, 2, 1] = -w[:, 0], -w[:, 1], w[:, 0]
+                th = theta[..., None]
+                I = torch.eye(3)[None]
+                Rm = I + torch.sin(th) * W + (1 - torch.cos(th)) * (W @ W)
+                p = (th * I + (1 - torch.cos(th)) * W + (th - torch.sin(th)) * (W @ W)) @ v[..., None]
+                top = torch.cat([Rm, p], -1)
+                d_xyz = torch.cat([top, torch.tensor([0., 0., 0., 1.]).expand(w.shape[0], 1, 4)], 1)
+            else:
+                d_xyz = self.gaussian_warp(h)
+            return d_xyz, self.gaussian_rotation(h), self.gaussian_scaling(h)
+
+    return Net()
+
+
+def workload_text(name, cfg, world):
+    if cfg["frames"] is None:
+        return "%s: %d Gaussians SH3 %dx%d deform MLP + rasterize fwd+bwd, 1 frame per GPU per step" % (
+            name, cfg["N"], cfg["W"], cfg["H"])
+    if cfg["train"]:
+        return ("%s: %d Gaussians SH3 %dx%d, %d-frame camera/time batch per step sharded over %d GPU(s), deform MLP "
+                "(one launch per rank) + rasterize fwd+bwd, one gradient all-reduce" % (
+                    name, cfg["N"], cfg["W"], cfg["H"], cfg["frames"], world))
+    return "%s: render-only, %d Gaussians SH3 %dx%d, %d-timestamp sweep split over %d GPU(s), no_grad, no collective" % (
+        name, cfg["N"], cfg["W"], cfg["H"], cfg["frames"], world)
 
 
 def run_reference(args, cfg, rank):
-    """--impl reference: the CPU restatement of the path on the host cores (the reference rasterizer has
-    no CPU path and its CUDA source is absent from the archive; the MLP half follows utils/time_utils.py)."""
+    """--impl reference: rank 0 alone runs the CPU arm on the full configuration."""
     if rank != 0:
         return
     arm = CpuArm(cfg)
-    sec = arm.time(args.steps, args.warmup)
+    sec, steps, warm = arm.time(args.steps, args.warmup, budget_s=float(os.environ.get("D3G_REF_BUDGET_S", "150")))
     fps = 1.0 / sec
     line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "%s: %d Gaussians SH3 %dx%d deform MLP + rasterize fwd+bwd, 1 frame" %
-                       (args.config, cfg["N"], cfg["W"], cfg["H"]), "is_6dof": cfg["is_6dof"]},
+            "steps": steps, "warmup": warm, "steps_requested": args.steps, "ms_per_step": sec * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_text(args.config, dict(cfg, frames=None), 1), "is_6dof": cfg["is_6dof"],
+                       "note": "one frame per step on the host cores; steps are capped so that the run ends within "
+                               "D3G_REF_BUDGET_S seconds and the steps actually timed are the ones reported"},
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": arm.cores, "kind": "port",
-                             "sample": arm.sample_text()},
+                             "sample": arm.sample_text(steps)},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+def pct(xs, q):
+    s = sorted(xs)
+    return s[min(len(s) - 1, max(0, int(round(q * (len(s) - 1)))))] if s else None
 
 
 def main():
@@ -414,61 +604,72 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=device)
-    work = Workload(cfg, rank, device)
+    work = Workload(cfg, rank, world, device)
 
-    for _ in range(max(args.warmup, 3)):
-        work.frame(False)
-        if world > 1:
-            work.grads.all_reduce()
+    warm = max(args.warmup, 3)
+    for _ in range(warm):
+        work.step(False)
+        work.exchange()
     sampler = ClockSampler(local_rank)
     sampler.start()
-    sec = timed_region(work, args.steps, False, world, dist)
-    work.frame(True)  # warm the host-copy path
+    sec, per_step = timed_region(work, args.steps, False, world, dist)
+    work.step(True)  # warm the host-copy path
     torch.cuda.synchronize()
     work.losses.clear()
-    sec_e2e = timed_region(work, args.steps, True, world, dist)
+    sec_e2e, per_step_e2e = timed_region(work, args.steps, True, world, dist)
     sampler.stop_flag = True
     sampler.join(timeout=2.0)
-    value = world * args.steps / sec
-    e2e = world * args.steps / sec_e2e
+    fps_step = work.frames_per_step
+    value = fps_step * args.steps / sec
+    e2e = fps_step * args.steps / sec_e2e
 
     line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": sec / args.steps * 1e3, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "tf32 (fp32 accumulate) MLP / f32 rasterizer",
-            "data": "synthetic",
-            "config": {"workload": "%s: %d Gaussians SH3 %dx%d deform MLP + rasterize fwd+bwd, 1 frame per GPU per step" %
-                       (args.config, cfg["N"], cfg["W"], cfg["H"]), "is_6dof": cfg["is_6dof"],
-                       "net": "DeformNetworkBaseline(is_blender=True)", "loss": "0.8*L1 + 0.2*(1-SSIM) vs fixed random image (fused CUDA loss)",
-                       "pair_capacity": "GrowingPairCapacity(1.1): no num_rendered read-back inside a frame",
-                       "l2": "per-step working set (saved MLP activation tiles, ~1.7 GB at 100k points) exceeds the 126 MB L2",
-                       "parallelism": "frame-parallel dp%d, one NCCL all-reduce of the flat gradient buffer, <= 2 frames in flight" % world},
+            "warmup": warm, "ms_per_step": sec / args.steps * 1e3, "higher_is_better": True,
+            "scaling": "weak" if cfg["frames"] is None else "strong", "vs_baseline": None,
+            "dtype": "f16 split x3 (fp32 accumulate, fp32-class accuracy) MLP / f32 rasterizer", "data": "synthetic",
+            "ms_per_step_percentiles": {"p10": pct(per_step, 0.1), "p50": pct(per_step, 0.5), "p90": pct(per_step, 0.9),
+                                        "note": "this rank's per-step CUDA-event intervals inside the timed region"},
+            "config": {"workload": workload_text(args.config, cfg, world), "is_6dof": cfg["is_6dof"],
+                       "frames_per_step": fps_step, "frames_per_rank": work.frames_per_rank,
+                       "busiest_rank_bound": ("ceil(%d/%d) = %d frames" % (fps_step, world, max(work.frames_per_rank))),
+                       "net": "DeformNetworkBaseline(is_blender=True)",
+                       "loss": ("0.8*L1 + 0.2*(1-SSIM) vs fixed random images (fused CUDA loss); multi-frame batches use "
+                                "the reference's cumulative-L1 frame weights (train.py:245-250)") if cfg["train"] else None,
+                       "pair_capacity": "GrowingPairCapacity: no num_rendered read-back inside a frame",
+                       "l2": "per-step working set (saved MLP activation tiles, ~0.9 GB per 100k points) exceeds the 126 MB L2",
+                       "parallelism": ("frame-parallel dp%d, one NCCL all-reduce of the flat gradient buffer, <= 2 steps in flight" % world)
+                       if cfg["train"] else ("timestamp-parallel x%d, no collective" % world)},
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": work.h2d_bytes, "d2h_bytes_per_step": 4,
-                    "ms_per_step": sec_e2e / args.steps * 1e3, "losses_read": len(work.losses),
-                    "last_loss": (work.losses[-1] if work.losses else None),
-                    "pipelining": "inputs uploaded from pinned memory and the loss copied to pinned memory every frame; "
-                                  "the host consumes frame k's loss while frame k+1 runs (<= 2 frames in flight)"},
+                    "ms_per_step": sec_e2e / args.steps * 1e3, "results_read": len(work.losses),
+                    "last_result": (work.losses[-1] if work.losses else None),
+                    "p10_p50_p90_ms": [pct(per_step_e2e, 0.1), pct(per_step_e2e, 0.5), pct(per_step_e2e, 0.9)],
+                    "pipelining": "inputs uploaded from pinned memory and the result copied to pinned memory every step; "
+                                  "the host consumes step k's result while step k+1 runs (<= 2 steps in flight)"},
             "clocks": sampler.summary()}
 
     if not args.no_roofline:
-        table, R = kernel_table(work, max(3, min(args.steps, 10)))
-        rows = roofline(table, R, cfg, peaks(), ncu_traffic(args.config))
+        table, R = kernel_table(work, max(2, min(args.steps, 10)))
+        rows_per_launch = cfg["N"] * (max(len(work.mine), 1) if cfg["train"] else min(4, max(len(work.mine), 1)))
+        rows = roofline(table, R, cfg, peaks(), rows_per_launch, ncu_traffic(args.config))
         line["gpu_launches"] = int(round(sum(r["launches_per_step"] for r in rows) * args.steps))
         line["pairs_R"] = R
         top = next((r for r in rows if r.get("bound")), None)
         if top:
             line["roofline"] = {"kernel": top["kernel"], "bound": top["bound"], "achieved": top["achieved"],
                                 "peak": top["peak"], "unit": top["unit"], "frac": top["frac"], "traffic": top["traffic"],
-                                "note": ("render_* are FP32-issue bound, not HBM bound: ncu sm__throughput 78-82 %, DRAM < 1 % "
-                                         "(profiles/r1z_top_kernels.md); GB/s against the HBM peak is reported because "
-                                         "the metric asks for it" if top["kernel"].startswith("render") else None),
-                                "peak_source": peaks()["source"] + (" bf16 sustained; kind::tf32 runs at half that rate"
+                                "note": ("render_* are FP32-issue bound, not HBM bound (ncu: sm__throughput ~80 %, DRAM "
+                                         "< 1 %, profiles/); GB/s against the HBM peak is reported because the metric "
+                                         "asks for it" if top["kernel"].startswith("render") else None),
+                                "peak_source": peaks()["source"] + (" bf16 sustained (kind::f16 runs at the bf16 rate); "
+                                                                    "tf32 dense measured 662 burst / 587 sustained "
+                                                                    "(profiles/r2_numerics_split.json)"
                                                                     if top["bound"] == "tensor" else " copy bandwidth")}
         line["kernels"] = [{k: (round(v, 5) if isinstance(v, float) else v) for k, v in r.items()} for r in rows]
     if world == 1 and rank == 0 and not args.no_cpu_baseline:
         arm = CpuArm(cfg)
-        csec = arm.time(2, 1)
+        csec, csteps, _ = arm.time(2, 1, budget_s=float(os.environ.get("D3G_CPU_BASELINE_BUDGET_S", "40")))
         line["cpu_baseline"] = {"value": 1.0 / csec, "unit": "frames/s", "cores": arm.cores, "kind": "port",
-                                "sample": arm.sample_text()}
+                                "sample": arm.sample_text(csteps)}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:

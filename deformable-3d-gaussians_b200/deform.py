@@ -205,8 +205,9 @@ class _FusedDeform(torch.autograd.Function):
 class _DeformBase(nn.Module):
     """Shared constructor: identical module tree to utils/time_utils.py:57-100 / :130-174."""
 
-    def __init__(self, D=8, W=256, input_ch=3, output_ch=59, multires=10, is_blender=False, is_6dof=False,
-                 rot_scale_heads=True):
+    _rot_scale_heads = True   # (DeformNetworkODE: warp head only)
+
+    def __init__(self, D=8, W=256, input_ch=3, output_ch=59, multires=10, is_blender=False, is_6dof=False):
         super().__init__()
         self.D, self.W = D, W
         self.output_ch = output_ch
@@ -233,7 +234,7 @@ class _DeformBase(nn.Module):
             self.branch_v = nn.Linear(W, 3)
         else:
             self.gaussian_warp = nn.Linear(W, 3)
-        if rot_scale_heads:
+        if self._rot_scale_heads:
             self.gaussian_rotation = nn.Linear(W, 4)
             self.gaussian_scaling = nn.Linear(W, 3)
         self.debug = bool(int(os.environ.get("D3G_DEBUG", "0")))
@@ -391,6 +392,7 @@ class DeformNetworkODE(_DeformBase):
     kernels; gradients flow to x, t and the parameters (the adjoint needs all three).  The use_linear 1..4 variants are
     single nn.Linear maps of the embedded input and stay torch ops, as in the reference."""
     _heads = HEAD_WARP
+    _rot_scale_heads = False
 
     def __init__(self, D=8, W=256, input_ch=3, output_ch=59, multires=10, is_blender=False, is_6dof=False,
                  use_linear=0, use_emb=True, output_scale=1, skips=[4]):
@@ -401,7 +403,7 @@ class DeformNetworkODE(_DeformBase):
                     "W=256, is_6dof=False (every configuration under arguments/); got use_emb=%s skips=%s D=%d W=%d "
                     "is_6dof=%s" % (use_emb, skips, D, W, is_6dof))
             super().__init__(D=D, W=W, input_ch=input_ch, output_ch=output_ch, multires=multires,
-                             is_blender=is_blender, is_6dof=False, rot_scale_heads=False)
+                             is_blender=is_blender, is_6dof=False)
             self.use_linear, self.use_emb, self.output_scale = use_linear, use_emb, output_scale
             return
         nn.Module.__init__(self)
