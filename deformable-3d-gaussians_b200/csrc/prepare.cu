@@ -172,3 +172,41 @@ extern "C" int d3g_gaussians_prepare_backward(int32_t N, int32_t is_6dof, const 
   D3G_LAUNCH_CHECK(0, stream);
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Densification bookkeeping of one rendered frame, fused:
+//   max_radii2D[vis] = max(max_radii2D[vis], radii[vis])                         (train.py:238-239)
+//   xyz_gradient_accum[vis] += || viewspace_grad[vis, :2] ||;  denom[vis] += 1   (scene/gaussian_model.py:398-401)
+// with vis = radii > 0 (gaussian_renderer/__init__.py:131).  One thread per Gaussian, one pass, no boolean-mask
+// gathers / scatters (the reference's indexed assignments are ~10 launches and two nonzero() syncs per frame).
+// ------------------------------------------------------------------------------------------------
+namespace d3g {
+__global__ void __launch_bounds__(256)
+densification_stats_kernel(int N, const float* __restrict__ vs_grad, const int* __restrict__ radii,
+                           float* __restrict__ accum, float* __restrict__ denom, float* __restrict__ max_radii) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  const int r = radii[i];
+  if (r <= 0) return;
+  if (max_radii) max_radii[i] = fmaxf(max_radii[i], (float)r);
+  if (vs_grad) {
+    const float gx = vs_grad[3 * (size_t)i], gy = vs_grad[3 * (size_t)i + 1];
+    accum[i] += sqrtf(gx * gx + gy * gy);
+    denom[i] += 1.0f;
+  }
+}
+}  // namespace d3g
+
+extern "C" int d3g_densification_stats(int32_t N, const float* viewspace_grad, const int32_t* radii,
+                                       float* xyz_gradient_accum, float* denom, float* max_radii2D, void* stream_) {
+  if (N < 0 || (N > 0 && !radii)) return d3g::set_err(D3G_ERR_INVALID, "densification_stats: radii is NULL");
+  if (viewspace_grad && (!xyz_gradient_accum || !denom))
+    return d3g::set_err(D3G_ERR_INVALID, "densification_stats: accumulators missing");
+  if (N == 0) return 0;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  { d3g::ProfScope _p(d3g::PROF_DENSIFY, stream);
+    d3g::densification_stats_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, viewspace_grad, radii, xyz_gradient_accum,
+                                                                       denom, max_radii2D);
+    D3G_LAUNCH_CHECK(0, stream); }
+  return 0;
+}

@@ -74,6 +74,30 @@ class FlatGrads:
         return self.flat
 
 
+def add_densification_stats(gaussians, render_pkg, update_max_radii=True):
+    """What the training loop does with one frame's render_pkg after backward — train.py:238-239 (`max_radii2D`) and
+    :283-284 -> GaussianModel.add_densification_stats (scene/gaussian_model.py:398-401) on
+    `viewspace_points_densify.grad` — as ONE kernel over the Gaussians instead of boolean-mask gathers and scatters.
+    `gaussians` needs the reference's `xyz_gradient_accum` [N,1], `denom` [N,1] and `max_radii2D` [N] tensors."""
+    import ctypes as C
+    from . import _lib
+    lib = _lib.load()
+    radii = render_pkg["radii"]
+    vs = render_pkg["viewspace_points_densify"].grad
+    if vs is not None and (vs.dtype != torch.float32 or not vs.is_contiguous()):
+        vs = vs.float().contiguous()
+    N = int(radii.shape[0])
+    acc, den, mr = gaussians.xyz_gradient_accum, gaussians.denom, gaussians.max_radii2D
+    for t in (acc, den, mr):
+        if t.dtype != torch.float32 or not t.is_contiguous() or t.device != radii.device:
+            raise RuntimeError("add_densification_stats: accumulators must be contiguous fp32 tensors on the "
+                               "rasterizer's device")
+    with torch.cuda.device(radii.device):
+        _lib.check(lib.d3g_densification_stats(N, _lib.ptr(vs), _lib.ptr(radii), _lib.ptr(acc), _lib.ptr(den),
+                                               _lib.ptr(mr) if update_max_radii else None,
+                                               C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+
+
 def reduce_densification_stats(grad_norm_accum, denom, max_radii2D, group=None):
     """Densification statistics are per-frame quantities (scene/gaussian_model.py:398-401 takes the norm of
     each frame's viewspace gradient BEFORE accumulating), so ranks reduce their local accumulators:

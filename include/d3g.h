@@ -165,6 +165,15 @@ typedef struct d3g_adam_tensor {
 int d3g_adam_step(int32_t n_tensors, const d3g_adam_tensor* tensors, double beta1, double beta2, double eps,
                   void* stream);
 
+/* Densification bookkeeping of one rendered frame in one launch: for every Gaussian with radii > 0 (the
+ * `visibility_filter` of gaussian_renderer/__init__.py:131)
+ *   max_radii2D = max(max_radii2D, radii)                                     (train.py:238-239)
+ *   xyz_gradient_accum += ||viewspace_grad[:, :2]||, denom += 1               (scene/gaussian_model.py:398-401)
+ * viewspace_grad: [N,3] (the .grad of `viewspace_points_densify` after backward) or NULL to update max_radii2D only;
+ * xyz_gradient_accum / denom: [N,1] fp32; max_radii2D: [N] fp32 or NULL. */
+int d3g_densification_stats(int32_t N, const float* viewspace_grad, const int32_t* radii,
+                            float* xyz_gradient_accum, float* denom, float* max_radii2D, void* stream);
+
 /* `simple_knn._C.distCUDA2` (submodules/simple-knn/spatial.cu:15-26 -> SimpleKNN::knn, simple_knn.cu:185-221; caller
  * scene/gaussian_model.py:105): mean_dist2[i] = mean of the three smallest squared distances from points[i] to the
  * points at the OTHER indices (exact; FLT_MAX stands in for a missing neighbour when P < 4, as in the reference).

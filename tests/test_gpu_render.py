@@ -213,3 +213,34 @@ def test_pipeline_6dof_end_to_end():
     diff = np.abs(out["render"].detach().cpu().numpy() - f["color"])
     # fp32 vs fp64 evaluation of the transform moves means by an ulp: allow isolated 1/255-threshold flips
     assert diff.mean() <= 1e-6 and diff.max() <= 5e-3
+
+
+def test_fused_densification_stats_match_reference_ops():
+    """frames.add_densification_stats (one kernel) against the reference's tensor ops: train.py:238-239 and
+    scene/gaussian_model.py:398-401, applied to a real render_pkg after backward."""
+    frames, synth, renderer = pkg("frames"), pkg("synth"), pkg("renderer")
+    dev = torch.device("cuda", 0)
+    N = 4000
+    g = synth.SynthGaussians(N, seed=5, sh_degree=3)
+    for name in ("_xyz", "_features_dc", "_features_rest", "_opacity", "_scaling", "_rotation"):
+        setattr(g, name, getattr(g, name).to(dev).requires_grad_(True))
+    cam = synth.camera_to(synth.make_camera(160, 120, theta_deg=40.0, fid=0.3), dev)
+    pipe = type("Pipe", (), dict(convert_SHs_python=False, compute_cov3D_python=False, debug=False))()
+    z3, z4 = torch.zeros(N, 3, device=dev), torch.zeros(N, 4, device=dev)
+    out = renderer.render(cam, g, pipe, torch.zeros(3, device=dev), z3, z4, z3)
+    (out["render"] * synth.image_cotangent(120, 160).to(dev)).sum().backward()
+    gen = torch.Generator().manual_seed(0)
+    acc0 = torch.rand(N, 1, generator=gen).to(dev)
+    den0 = torch.randint(0, 5, (N, 1), generator=gen).float().to(dev)
+    mr0 = (torch.rand(N, generator=gen) * 6).to(dev)
+    # reference ops
+    vis, radii = out["visibility_filter"], out["radii"]
+    assert 0 < int(vis.sum()) < N
+    acc_r, den_r, mr_r = acc0.clone(), den0.clone(), mr0.clone()
+    mr_r[vis] = torch.max(mr_r[vis], radii[vis].float())
+    acc_r[vis] += torch.norm(out["viewspace_points_densify"].grad[vis, :2], dim=-1, keepdim=True)
+    den_r[vis] += 1
+    g.xyz_gradient_accum, g.denom, g.max_radii2D = acc0.clone(), den0.clone(), mr0.clone()
+    frames.add_densification_stats(g, out)
+    assert torch.equal(g.max_radii2D, mr_r) and torch.equal(g.denom, den_r)
+    assert torch.allclose(g.xyz_gradient_accum, acc_r, rtol=1e-6, atol=0)
