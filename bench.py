@@ -42,6 +42,8 @@ CONFIGS = {
     "C3": dict(N=300000, H=800, W=800, is_6dof=False, kind="uniform", frames=10, train=True),
     "C4": dict(N=200000, H=800, W=800, is_6dof=True, kind="uniform", frames=None, train=True),
     "C5": dict(N=1000000, H=1080, W=1920, is_6dof=False, kind="uniform", frames=100, train=False),
+    # diagnostic only: a frame so small that the step time is the host-side launch overhead of the path
+    "host": dict(N=2000, H=64, W=64, is_6dof=False, kind="uniform", frames=None, train=True),
 }
 METRIC = "deform+raster fwd+bwd frames/sec @100k Gaussians 800x800, 1/2/4/8 B200"
 LAMBDA_DSSIM = 0.2   # arguments/__init__.py:119

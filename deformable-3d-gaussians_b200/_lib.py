@@ -72,7 +72,7 @@ class RasterSettings(C.Structure):
                 ("tanfovy", C.c_float), ("bg", C.c_void_p), ("scale_modifier", C.c_float),
                 ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("sh_degree", C.c_int32),
                 ("campos", C.c_void_p), ("prefiltered", C.c_int32), ("debug", C.c_int32),
-                ("densify_mode", C.c_int32)]
+                ("densify_mode", C.c_int32), ("binning_mode", C.c_int32)]
 
 
 class AdamTensor(C.Structure):

@@ -20,6 +20,7 @@ namespace d3g {
 
 static constexpr int kTile = 16;
 static constexpr int kBlock = kTile * kTile;
+static constexpr int kTileCtrStride = 32;   // uint32 words between the counters of consecutive tiles (128 B)
 
 struct GeomView {
   uint32_t* header;  // [0]=R [1]=overflow
@@ -104,6 +105,8 @@ struct ImgView {
   uint2* ranges;
   float* final_T;
   uint32_t* n_contrib;
+  uint32_t* tile_count;    // tile binning: pairs per tile
+  uint32_t* tile_cursor;   // tile binning: write cursor of each tile's segment
   size_t total;
 };
 
@@ -117,6 +120,10 @@ static ImgView img_view(void* base, int H, int W) {
   v.ranges = (uint2*)take((tiles ? tiles : 1) * 8);
   v.final_T = (float*)take((P ? P : 1) * 4);
   v.n_contrib = (uint32_t*)take((P ? P : 1) * 4);
+  // one 128-byte line per tile ([0] = count, [1] = cursor): the per-pair atomics of neighbouring tiles then land on
+  // different L2 lines instead of serialising on 80 hot ones (measured 90 us -> see DESIGN.md for count / scatter)
+  v.tile_count = (uint32_t*)take((tiles ? tiles : 1) * kTileCtrStride * 4);
+  v.tile_cursor = v.tile_count + 1;
   v.total = off;
   return v;
 }
@@ -284,7 +291,7 @@ __device__ __forceinline__ void sh_basis(int deg, const float d[3], float b[16])
 }
 
 struct RasterArgs {
-  int N, H, W, gx, gy, sh_degree, M, densify_mode;
+  int N, H, W, gx, gy, sh_degree, M, densify_mode, binning_mode;
   float tanfovx, tanfovy, scale_modifier;
   const float* bg;
   const float* view;
@@ -302,7 +309,8 @@ preprocess_fwd_kernel(RasterArgs a, const float* __restrict__ means3D, const flo
                       const float* __restrict__ cov3D_precomp, int32_t* __restrict__ radii,
                       float2* __restrict__ means2D, float4* __restrict__ conic_opacity,
                       float4* __restrict__ rgbd, float* __restrict__ cov3D,
-                      uint32_t* __restrict__ tiles_touched, uint8_t* __restrict__ clamped) {
+                      uint32_t* __restrict__ tiles_touched, uint8_t* __restrict__ clamped,
+                      uint32_t* __restrict__ pair_counter) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= a.N) return;
   int radius_out = 0;
@@ -411,6 +419,11 @@ preprocess_fwd_kernel(RasterArgs a, const float* __restrict__ means3D, const flo
   for (int k = 0; k < 6; k++) cov3D[6 * (size_t)i + k] = cov6[k];
   tiles_touched[i] = tiles;
   clamped[i] = clamp_bits;
+  if (pair_counter) {   // tile binning: R = sum of tiles_touched without a scan over the Gaussians
+    const unsigned m = __activemask();
+    const uint32_t sum = __reduce_add_sync(m, tiles);
+    if ((threadIdx.x & 31) == (__ffs(m) - 1) && sum) atomicAdd(pair_counter, sum);
+  }
 }
 
 __global__ void finish_scan_kernel(int N, const uint32_t* __restrict__ offsets, uint32_t* header) {
@@ -470,6 +483,230 @@ identify_tile_ranges_kernel(uint64_t cap, const uint32_t* __restrict__ header,
     if (tile != prev) { ranges[prev].y = (uint32_t)j; ranges[tile].x = (uint32_t)j; }
   }
   if (j == R - 1) ranges[tile].y = (uint32_t)R;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Tile binning (binning_mode 0, the default): the same sorted (tile | depth) list, point list and tile ranges as
+// duplicateWithKeys + 64-bit radix sort + identifyTileRanges, without sorting the tile bits and without six
+// 8-bit passes over all pairs:
+//   count   : one atomic per (tile, Gaussian) pair on the tile's counter
+//   scan    : exclusive scan of the tile counters = the tile ranges (empty tiles stay (0,0) as in the reference)
+//   scatter : each pair takes the next slot of its tile's segment and stores (depth bits << 32 | Gaussian index)
+//   sort    : one CTA per tile sorts its segment in shared memory by that 64-bit key.  The keys of a tile are
+//             unique, and the reference's stable sort of (tile | depth) leaves equal keys in emission order =
+//             ascending Gaussian index, so the result is bit-identical to the radix path.
+// Segments longer than kTileSortCap are sorted in chunks and merged through global memory by the same CTA.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+tile_count_kernel(int N, int gx, int gy, const float2* __restrict__ means2D, const int32_t* __restrict__ radii,
+                  uint32_t* __restrict__ tile_count) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  int r = radii[i];
+  if (r <= 0) return;
+  float2 m = means2D[i];
+  int mnx, mny, mxx, mxy;
+  get_rect(m.x, m.y, r, gx, gy, mnx, mny, mxx, mxy);
+  for (int y = mny; y < mxy; y++)
+    for (int x = mnx; x < mxx; x++) atomicAdd(&tile_count[(size_t)(y * gx + x) * kTileCtrStride], 1u);
+}
+
+// single CTA: exclusive scan of the tile counters -> ranges, cursors; checks R against the capacity
+__global__ void __launch_bounds__(1024)
+tile_scan_kernel(int tiles, uint64_t cap, const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_cursor,
+                 uint2* __restrict__ ranges, uint32_t* __restrict__ header) {
+  __shared__ uint32_t s_warp[32];
+  __shared__ uint32_t s_carry;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_carry = 0;
+  __syncthreads();
+  const int per = (tiles + 1023) / 1024;
+  const int t0 = tid * per, t1 = min(tiles, t0 + per);
+  uint32_t local = 0;
+  for (int t = t0; t < t1; t++) local += tile_count[(size_t)t * kTileCtrStride];
+  uint32_t inc = local;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+  if (lane == 31) s_warp[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t w = s_warp[lane], winc = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(0xffffffffu, winc, o); if (lane >= o) winc += v; }
+    s_warp[lane] = winc - w;
+    if (lane == 31) s_carry = winc;
+  }
+  __syncthreads();
+  uint32_t off = s_warp[warp] + inc - local;
+  const uint32_t R = s_carry;
+  const bool overflow = (uint64_t)R > cap;
+  for (int t = t0; t < t1; t++) {
+    const uint32_t c = tile_count[(size_t)t * kTileCtrStride];
+    tile_cursor[(size_t)t * kTileCtrStride] = off;
+    ranges[t] = (c && !overflow) ? make_uint2(off, off + c) : make_uint2(0u, 0u);
+    off += c;
+  }
+  if (tid == 0) { header[0] = R; header[1] = overflow ? 1u : 0u; }
+}
+
+// The slot of a pair is the return value of an atomic.  One thread per Gaussian walking its own tiles makes a latency
+// chain as long as the largest splat of the warp (measured 105 us at C2, 62 us with eight atomics in flight per
+// thread).  Here a warp flattens the pairs of its 32 Gaussians: pair p of the warp goes to lane p % 32, which finds
+// the owning Gaussian in the warp's prefix sums by shuffles; every lane keeps four independent atomics in flight.
+__global__ void __launch_bounds__(256)
+tile_scatter_kernel(int N, int gx, int gy, const float2* __restrict__ means2D, const float4* __restrict__ rgbd,
+                    const int32_t* __restrict__ radii, uint32_t* __restrict__ tile_cursor,
+                    uint64_t* __restrict__ seg, const uint32_t* __restrict__ header) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  if (header[1]) return;
+  int mnx = 0, mny = 0, w = 0, cnt = 0;
+  uint32_t depth_bits = 0;
+  if (i < N) {
+    const int r = radii[i];
+    if (r > 0) {
+      const float2 m = means2D[i];
+      int mxx, mxy;
+      get_rect(m.x, m.y, r, gx, gy, mnx, mny, mxx, mxy);
+      w = mxx - mnx;
+      cnt = w * (mxy - mny);
+      depth_bits = __float_as_uint(rgbd[i].w);
+    }
+  }
+  int incl = cnt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+  const int total = __shfl_sync(0xffffffffu, incl, 31);
+  for (int p0 = 0; p0 < total; p0 += 128) {
+    uint32_t pos[4], owner[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int p = p0 + k * 32 + lane;
+      // owner = first lane whose inclusive prefix exceeds p (lower bound over 32 lanes, 5 shuffle steps)
+      int lo = 0;
+#pragma unroll
+      for (int step = 16; step > 0; step >>= 1) {
+        const int v = __shfl_sync(0xffffffffu, incl, lo + step - 1);
+        if (v <= p) lo += step;
+      }
+      const int o_incl = __shfl_sync(0xffffffffu, incl, lo), o_cnt = __shfl_sync(0xffffffffu, cnt, lo);
+      const int o_w = __shfl_sync(0xffffffffu, w, lo), o_x = __shfl_sync(0xffffffffu, mnx, lo);
+      const int o_y = __shfl_sync(0xffffffffu, mny, lo);
+      owner[k] = (uint32_t)lo;
+      pos[k] = 0xFFFFFFFFu;
+      if (p < total) {
+        const int t = p - (o_incl - o_cnt);
+        const int y = o_y + t / o_w, x = o_x + t % o_w;
+        pos[k] = atomicAdd(&tile_cursor[(size_t)(y * gx + x) * kTileCtrStride], 1u);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const uint32_t d = __shfl_sync(0xffffffffu, depth_bits, owner[k]);
+      if (pos[k] != 0xFFFFFFFFu)
+        seg[pos[k]] = ((uint64_t)d << 32) | (uint32_t)(i - lane + (int)owner[k]);
+    }
+  }
+}
+
+static constexpr int kTileSortCap = 4096;   // keys sorted in shared memory at once (32 KB)
+
+// bitonic sort of n_pad (power of two <= kTileSortCap) 64-bit keys in shared memory, ascending
+// (steps with partner distance < 64 stay inside an aligned block of 64 keys: one warp runs all of them for its
+// blocks back to back with __syncwarp only; block-wide barriers are needed for the longer-distance steps alone)
+__device__ __forceinline__ void smem_bitonic(uint64_t* k, int n_pad) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  for (int size = 2; size <= n_pad; size <<= 1) {
+    int j = size >> 1;
+    for (; j >= 64; j >>= 1) {
+      for (int t = threadIdx.x; t < (n_pad >> 1); t += blockDim.x) {
+        const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), p = i | j;
+        const uint64_t a = k[i], b = k[p];
+        if ((a > b) == ((i & size) == 0)) { k[i] = b; k[p] = a; }
+      }
+      __syncthreads();
+    }
+    for (int blk = warp; blk < ((n_pad + 63) >> 6); blk += nwarps) {
+      const int base = blk << 6;
+      for (int jj = j; jj > 0; jj >>= 1) {
+        const int i = base + (((lane & ~(jj - 1)) << 1) | (lane & (jj - 1))), p = i | jj;
+        if (p < n_pad) {
+          const uint64_t a = k[i], b = k[p];
+          if ((a > b) == ((i & size) == 0)) { k[i] = b; k[p] = a; }
+        }
+        __syncwarp();
+      }
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(256)
+tile_sort_kernel(const uint2* __restrict__ ranges, uint64_t* seg, uint64_t* tmp, uint64_t* keys_sorted,
+                 uint32_t* __restrict__ point_list) {
+  extern __shared__ __align__(16) uint64_t s_keys[];
+  const uint32_t tile = blockIdx.x;
+  const uint2 rg = ranges[tile];
+  const int n = (int)(rg.y - rg.x);
+  if (n <= 0) return;
+  uint64_t* src = seg + rg.x;
+  if (n <= kTileSortCap) {
+    int n_pad = 2;
+    while (n_pad < n) n_pad <<= 1;
+    for (int i = threadIdx.x; i < n_pad; i += blockDim.x) s_keys[i] = i < n ? src[i] : ~0ull;
+    __syncthreads();
+    smem_bitonic(s_keys, n_pad);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const uint64_t r = s_keys[i];
+      keys_sorted[rg.x + i] = ((uint64_t)tile << 32) | (r >> 32);
+      point_list[rg.x + i] = (uint32_t)r;
+    }
+    return;
+  }
+  // long segment: sort chunks of kTileSortCap in shared memory, then merge runs pairwise through global memory
+  uint64_t* dst = tmp + rg.x;
+  for (int c0 = 0; c0 < n; c0 += kTileSortCap) {
+    const int m = min(kTileSortCap, n - c0);
+    for (int i = threadIdx.x; i < kTileSortCap; i += blockDim.x) s_keys[i] = i < m ? src[c0 + i] : ~0ull;
+    __syncthreads();
+    smem_bitonic(s_keys, kTileSortCap);
+    for (int i = threadIdx.x; i < m; i += blockDim.x) src[c0 + i] = s_keys[i];
+    __syncthreads();
+  }
+  for (int run = kTileSortCap; run < n; run <<= 1) {
+    __threadfence_block();
+    __syncthreads();
+    // each thread produces a contiguous slice of every merged pair of runs (merge path by binary search)
+    for (int base = 0; base < n; base += 2 * run) {
+      const int la = min(run, n - base), lb = max(0, min(run, n - base - run));
+      const uint64_t* A = src + base;
+      const uint64_t* B = src + base + la;
+      const int total = la + lb;
+      const int per = (total + (int)blockDim.x - 1) / (int)blockDim.x;
+      const int o0 = min(total, (int)threadIdx.x * per), o1 = min(total, o0 + per);
+      if (o0 < o1) {
+        int lo = max(0, o0 - lb), hi = min(o0, la);   // elements taken from A among the first o0 outputs
+        while (lo < hi) {
+          const int mid = (lo + hi) >> 1;
+          if (A[mid] <= B[o0 - mid - 1]) lo = mid + 1; else hi = mid;
+        }
+        int ia = lo, ib = o0 - lo;
+        for (int o = o0; o < o1; o++) {
+          const bool takeA = ib >= lb || (ia < la && A[ia] <= B[ib]);
+          dst[base + o] = takeA ? A[ia++] : B[ib++];
+        }
+      }
+    }
+    __threadfence_block();
+    __syncthreads();
+    uint64_t* t = src; src = dst; dst = t;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const uint64_t r = src[i];
+    keys_sorted[rg.x + i] = ((uint64_t)tile << 32) | (r >> 32);
+    point_list[rg.x + i] = (uint32_t)r;
+  }
 }
 
 // Conservative early-out for the blend loops.  A Gaussian contributes to a pixel only if
@@ -1062,6 +1299,7 @@ static RasterArgs make_args(const d3g_raster_settings* s, int N, int M) {
   a.gx = (a.W + kTile - 1) / kTile; a.gy = (a.H + kTile - 1) / kTile;
   a.sh_degree = s->sh_degree; a.M = M;
   a.densify_mode = s->densify_mode ? s->densify_mode : 2;
+  a.binning_mode = s->binning_mode;
   a.tanfovx = s->tanfovx; a.tanfovy = s->tanfovy; a.scale_modifier = s->scale_modifier;
   a.bg = s->bg; a.view = s->viewmatrix; a.proj = s->projmatrix; a.campos = s->campos;
   return a;
@@ -1113,15 +1351,19 @@ int d3g_raster_preprocess(const d3g_raster_settings* s, int32_t N, const float* 
   RasterArgs a = make_args(s, N, M);
   if (N > 0) {
     { ProfScope _p(PROF_PREPROCESS_FWD, stream);
+    const bool tile_mode = a.binning_mode == 0;
+    if (tile_mode) D3G_CUDA_TRY(cudaMemsetAsync(g.header, 0, 8, stream));
     preprocess_fwd_kernel<<<(N + 255) / 256, 256, 0, stream>>>(
         a, means3D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp, radii, g.means2D,
-        g.conic_opacity, g.rgbd, g.cov3D, g.tiles_touched, g.clamped);
+        g.conic_opacity, g.rgbd, g.cov3D, g.tiles_touched, g.clamped, tile_mode ? g.header : nullptr);
     D3G_LAUNCH_CHECK(s->debug, stream); }
-    size_t tb = g.scan_temp_bytes;
-    ProfScope _p(PROF_SCAN, stream);
-    D3G_CUDA_TRY(cub::DeviceScan::InclusiveSum(g.scan_temp, tb, g.tiles_touched, g.offsets, N, stream));
-    finish_scan_kernel<<<1, 1, 0, stream>>>(N, g.offsets, g.header);
-    D3G_LAUNCH_CHECK(s->debug, stream);
+    if (a.binning_mode != 0) {   // the reference's own scheme needs the per-Gaussian offsets
+      size_t tb = g.scan_temp_bytes;
+      ProfScope _p(PROF_SCAN, stream);
+      D3G_CUDA_TRY(cub::DeviceScan::InclusiveSum(g.scan_temp, tb, g.tiles_touched, g.offsets, N, stream));
+      finish_scan_kernel<<<1, 1, 0, stream>>>(N, g.offsets, g.header);
+      D3G_LAUNCH_CHECK(s->debug, stream);
+    }
   } else {
     finish_scan_kernel<<<1, 1, 0, stream>>>(N, g.offsets, g.header);
     D3G_LAUNCH_CHECK(s->debug, stream);
@@ -1145,8 +1387,31 @@ int d3g_raster_render(const d3g_raster_settings* s, int32_t N, uint64_t cap, voi
   RasterArgs a = make_args(s, N, 0);
   size_t tiles = (size_t)a.gx * a.gy;
   if (tiles == 0) return 0;
-  D3G_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, tiles * sizeof(uint2), stream));
-  if (cap > 0 && N > 0) {
+  if (a.binning_mode == 0 && N > 0) {
+    if (tiles > 0x7fffffffu) return set_err(D3G_ERR_CAPACITY, "too many tiles");
+    D3G_CUDA_TRY(cudaMemsetAsync(im.tile_count, 0, tiles * kTileCtrStride * sizeof(uint32_t), stream));
+    { ProfScope _p(PROF_DUPLICATE, stream);
+      tile_count_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, a.gx, a.gy, g.means2D, radii, im.tile_count);
+      D3G_LAUNCH_CHECK(s->debug, stream); }
+    { ProfScope _p(PROF_SCAN, stream);
+      tile_scan_kernel<<<1, 1024, 0, stream>>>((int)tiles, cap, im.tile_count, im.tile_cursor, im.ranges, g.header);
+      D3G_LAUNCH_CHECK(s->debug, stream); }
+    if (cap > 0) {
+      { ProfScope _p(PROF_DUPLICATE, stream);
+        tile_scatter_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, a.gx, a.gy, g.means2D, g.rgbd, radii, im.tile_cursor,
+                                                               b.keys_unsorted, g.header);
+        D3G_LAUNCH_CHECK(s->debug, stream); }
+      { ProfScope _p(PROF_TILE_SORT, stream);
+        // (the keys_sorted buffer doubles as the merge scratch of long segments: every element is finally rewritten
+        // in place by the thread that read it)
+        tile_sort_kernel<<<(unsigned)tiles, 256, kTileSortCap * sizeof(uint64_t), stream>>>(
+            im.ranges, b.keys_unsorted, b.keys_sorted, b.keys_sorted, b.point_list);
+        D3G_LAUNCH_CHECK(s->debug, stream); }
+    }
+  } else {
+    D3G_CUDA_TRY(cudaMemsetAsync(im.ranges, 0, tiles * sizeof(uint2), stream));
+  }
+  if (a.binning_mode != 0 && cap > 0 && N > 0) {
     { ProfScope _p(PROF_DUPLICATE, stream);
     duplicate_with_keys_kernel<<<(N + 255) / 256, 256, 0, stream>>>(
         N, a.gx, a.gy, cap, g.means2D, g.rgbd, g.offsets, radii, b.keys_unsorted, b.vals_unsorted, g.header);

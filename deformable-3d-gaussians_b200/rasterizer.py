@@ -35,6 +35,11 @@ class GaussianRasterizationSettings(NamedTuple):
 # Semantics of means2D_densify.grad (DESIGN.md "open semantic #1"); 2 = sum of |per-pixel term|.
 DENSIFY_MODE = 2
 
+# How the (tile, Gaussian) pairs are binned: 0 = per-tile binning (default), 1 = the reference's duplicateWithKeys +
+# 64-bit radix sort + identifyTileRanges.  Both give bit-identical sorted keys, point list and tile ranges
+# (tests/test_gpu_raster.py); the unsorted key list and the per-Gaussian offsets only exist in mode 1.
+BINNING_MODE = 0
+
 # Optional sync-free operation: when set to a callable (N, H, W) -> pair capacity, forward sizes the
 # binning workspace from it instead of reading the pair count back from the device.
 PAIR_CAPACITY_POLICY = None
@@ -119,6 +124,7 @@ def _settings_struct(rs, keep):
     s.sh_degree = int(rs.sh_degree)
     s.prefiltered, s.debug = int(bool(rs.prefiltered)), int(bool(rs.debug))
     s.densify_mode = DENSIFY_MODE
+    s.binning_mode = BINNING_MODE
     return s
 
 

@@ -71,6 +71,10 @@ typedef struct d3g_raster_settings {
   int32_t densify_mode;    /* semantics of means2D_densify.grad: 1 = same as means2D.grad,
                               2 = component-wise sum of |per-pixel term| (default), 3 = sum of per-pixel
                               2-norms in .x.  See DESIGN.md "open semantic #1". */
+  int32_t binning_mode;    /* 0 (default): per-tile binning — count, scan over tiles, scatter, one shared-memory sort
+                              per tile; 1: the reference's scheme — duplicateWithKeys + one 64-bit radix sort +
+                              identifyTileRanges.  Sorted keys, point list and tile ranges are bit-identical; the
+                              unsorted key/value lists and the per-Gaussian offsets exist only in mode 1. */
 } d3g_raster_settings;
 
 /* Workspace sizes (bytes).  geom: per-Gaussian state; img: per-pixel + per-tile state;

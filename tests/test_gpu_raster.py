@@ -34,9 +34,10 @@ def _oracle(g, cam, bg, H, W, densify_mode=2, means3D=None, colors=None, cov=Non
     return cfg, f
 
 
-def _gpu_forward(g, cam, bg, H, W, colors=None, cov=None, requires_grad=False):
+def _gpu_forward(g, cam, bg, H, W, colors=None, cov=None, requires_grad=False, binning=0):
     rast = pkg("rasterizer")
     synth = pkg("synth")
+    rast.BINNING_MODE = binning   # 0: per-tile binning (default), 1: the reference's 64-bit radix sort
     camd = synth.camera_to(cam, "cuda")
     rs = rast.GaussianRasterizationSettings(
         image_height=H, image_width=W, tanfovx=math.tan(cam.FoVx * 0.5), tanfovy=math.tan(cam.FoVy * 0.5),
@@ -51,16 +52,20 @@ def _gpu_forward(g, cam, bg, H, W, colors=None, cov=None, requires_grad=False):
     m2d = torch.zeros(N, 3, device="cuda", requires_grad=True)
     m2dd = torch.zeros(N, 3, device="cuda", requires_grad=True)
     r = rast.GaussianRasterizer(rs)
-    color, radii, depth = r(means2D=m2d, means2D_densify=m2dd, **inp)
+    try:
+        color, radii, depth = r(means2D=m2d, means2D_densify=m2dd, **inp)
+    finally:
+        rast.BINNING_MODE = 0
     return color, radii, depth, rast._RasterizeGaussians.last_state, inp, m2d, m2dd
 
 
-def _check_forward_bitexact(f, color, radii, depth, st):
+def _check_forward_bitexact(f, color, radii, depth, st, binning=0):
     N, R = f["N"], f["R"]
     assert st.R == R, "duplication count R"
     assert np.array_equal(radii.cpu().numpy(), f["radii"]), "radii"
     assert np.array_equal(st.read(5, torch.int32, N).numpy().view(np.uint32), f["tiles_touched"]), "tiles_touched"
-    assert np.array_equal(st.read(6, torch.int32, N).numpy().view(np.uint32), f["offsets"]), "offsets"
+    if binning == 1:   # the per-Gaussian offsets and the unsorted pair list exist only in the reference's scheme
+        assert np.array_equal(st.read(6, torch.int32, N).numpy().view(np.uint32), f["offsets"]), "offsets"
     assert np.array_equal(st.read(0, torch.float32, 2 * N).numpy().reshape(N, 2).view(np.uint32),
                           f["means2D"].view(np.uint32)), "means2D bits"
     assert np.array_equal(st.read(1, torch.float32, N).numpy().view(np.uint32), f["depths"].view(np.uint32)), "depth bits"
@@ -71,7 +76,8 @@ def _check_forward_bitexact(f, color, radii, depth, st):
     cl = st.read(7, torch.uint8, N).numpy()
     assert np.array_equal(cl, f["clamped"][:, 0] | (f["clamped"][:, 1] << 1) | (f["clamped"][:, 2] << 2)), "clamped"
     if R:
-        assert np.array_equal(st.read(13, torch.int64, R).numpy().view(np.uint64), f["keys_unsorted"][:R]), "unsorted keys"
+        if binning == 1:
+            assert np.array_equal(st.read(13, torch.int64, R).numpy().view(np.uint64), f["keys_unsorted"][:R]), "unsorted keys"
         assert np.array_equal(st.read(8, torch.int64, R).numpy().view(np.uint64), f["keys"][:R]), "sorted keys"
         assert np.array_equal(st.read(9, torch.int32, R).numpy().view(np.uint32), f["point_list"][:R]), "point list"
     T = f["ranges"].shape[0]
@@ -95,11 +101,38 @@ def _check_forward_bitexact(f, color, radii, depth, st):
     (50000, 400, 400, "blob", 1.0, 3),       # config C1
     (100000, 800, 800, "uniform", 1.0, 3),   # config C2 at full size
 ])
-def test_forward_bit_exact(N, H, W, kind, scale_mul, deg):
+@pytest.mark.parametrize("binning", [0, 1])
+def test_forward_bit_exact(N, H, W, kind, scale_mul, deg, binning):
     g, cam, bg = _scene(N, H, W, seed=N, kind=kind, scale_mul=scale_mul, sh_degree=deg)
     _, f = _oracle(g, cam, bg, H, W)
-    color, radii, depth, st, *_ = _gpu_forward(g, cam, bg, H, W)
-    _check_forward_bitexact(f, color, radii, depth, st)
+    color, radii, depth, st, *_ = _gpu_forward(g, cam, bg, H, W, binning=binning)
+    _check_forward_bitexact(f, color, radii, depth, st, binning)
+
+
+@pytest.mark.parametrize("N,H,W,kind,scale_mul", [
+    (30000, 64, 64, "blob", 4.0),       # ~16 tiles with far more than 4096 pairs each: chunked sort + global merges
+    (60000, 96, 80, "uniform", 3.0),
+    (3000, 128, 128, "uniform", 1.0),
+])
+def test_tile_binning_equals_radix_binning(N, H, W, kind, scale_mul):
+    """Per-tile binning (count / scan / scatter / shared-memory sort, with the merge path for long segments) against
+    the reference's duplicateWithKeys + 64-bit radix sort: sorted keys, point list, tile ranges and image identical."""
+    g, cam, bg = _scene(N, H, W, seed=N + 1, kind=kind, scale_mul=scale_mul)
+    outs = []
+    for mode in (1, 0):
+        with torch.no_grad():
+            color, radii, depth, st, *_ = _gpu_forward(g, cam, bg, H, W, binning=mode)
+        R = st.R
+        T = ((W + 15) // 16) * ((H + 15) // 16)
+        outs.append((R, st.read(8, torch.int64, R).numpy(), st.read(9, torch.int32, R).numpy(),
+                     st.read(10, torch.int32, 2 * T).numpy(), color.cpu().numpy(), depth.cpu().numpy()))
+    a, b = outs
+    assert a[0] == b[0] and a[0] > 0
+    if N == 30000:
+        counts = np.bincount((a[1].view(np.uint64) >> np.uint64(32)).astype(np.int64))
+        assert counts.max() > 2 * 4096, counts.max()    # the long-segment path really ran
+    for x, y, name in zip(a[1:], b[1:], ("sorted keys", "point list", "ranges", "image", "depth")):
+        assert np.array_equal(x, y), name
 
 
 def _rel(a, b):
@@ -209,30 +242,33 @@ def test_mark_visible():
     assert np.mean(vis == (z > 0.2)) > 0.999
 
 
+@pytest.mark.parametrize("binning", [0, 1])
 @pytest.mark.parametrize("N,H,W", [(200000, 800, 800), (1000000, 1080, 1920)])  # C4 / C5 sizes
-def test_full_size_properties(N, H, W):
+def test_full_size_properties(N, H, W, binning):
     """Size-independent invariants at the sizes the oracle is too slow for: scan/duplication counts agree,
     the sort is a stable-order permutation of the unsorted pairs (sortedness + checksum of checksums), tile
     ranges partition the sorted list, per-pixel state is within bounds, and the path is deterministic."""
     g, cam, bg = _scene(N, H, W, seed=7)
     with torch.no_grad():
-        color, radii, depth, st, *_ = _gpu_forward(g, cam, bg, H, W)
+        color, radii, depth, st, *_ = _gpu_forward(g, cam, bg, H, W, binning=binning)
     R = st.R
     tiles_touched = st.read(5, torch.int32, N).numpy().view(np.uint32).astype(np.int64)
-    offsets = st.read(6, torch.int32, N).numpy().view(np.uint32).astype(np.int64)
-    assert tiles_touched.sum() == R and offsets[-1] == R
-    assert np.array_equal(np.cumsum(tiles_touched), offsets)
+    assert tiles_touched.sum() == R
     assert np.array_equal(radii.cpu().numpy() > 0, tiles_touched > 0)
-    ku = st.read(13, torch.int64, R).numpy().view(np.uint64)
-    vu = st.read(14, torch.int32, R).numpy().view(np.uint32)
     ks = st.read(8, torch.int64, R).numpy().view(np.uint64)
     vs = st.read(9, torch.int32, R).numpy().view(np.uint32)
     assert np.all(ks[1:] >= ks[:-1]), "sortedness"
-    # permutation: same multiset of (key, value) pairs — wrap-around sums of keys, values and a mixed hash
-    mix = lambda k, v: (k * np.uint64(0x9E3779B97F4A7C15)) ^ (v.astype(np.uint64) * np.uint64(0xC2B2AE3D27D4EB4F))
-    with np.errstate(over="ignore"):
-        assert ku.sum() == ks.sum() and vu.astype(np.uint64).sum() == vs.astype(np.uint64).sum()
-        assert mix(ku, vu).sum() == mix(ks, vs).sum(), "checksum of (key,value) pairs"
+    assert np.array_equal(np.bincount(vs, minlength=N), tiles_touched), "every Gaussian appears tiles_touched times"
+    if binning == 1:
+        offsets = st.read(6, torch.int32, N).numpy().view(np.uint32).astype(np.int64)
+        assert offsets[-1] == R and np.array_equal(np.cumsum(tiles_touched), offsets)
+        ku = st.read(13, torch.int64, R).numpy().view(np.uint64)
+        vu = st.read(14, torch.int32, R).numpy().view(np.uint32)
+        # permutation: same multiset of (key, value) pairs — wrap-around sums of keys, values and a mixed hash
+        mix = lambda k, v: (k * np.uint64(0x9E3779B97F4A7C15)) ^ (v.astype(np.uint64) * np.uint64(0xC2B2AE3D27D4EB4F))
+        with np.errstate(over="ignore"):
+            assert ku.sum() == ks.sum() and vu.astype(np.uint64).sum() == vs.astype(np.uint64).sum()
+            assert mix(ku, vu).sum() == mix(ks, vs).sum(), "checksum of (key,value) pairs"
     # the pair -> key map is intact: key of a sorted entry = (its tile, depth bits of its Gaussian)
     depths = st.read(1, torch.float32, N).numpy().view(np.uint32)
     assert np.array_equal((ks & np.uint64(0xFFFFFFFF)).astype(np.uint32), depths[vs])
@@ -254,7 +290,7 @@ def test_full_size_properties(N, H, W):
     # black background: image = sum of non-negative colours * weights; depth = sum of positive depths * weights
     assert color.min().item() >= 0 and depth.min().item() >= 0
     with torch.no_grad():
-        color2, radii2, depth2, *_ = _gpu_forward(g, cam, bg, H, W)
+        color2, radii2, depth2, *_ = _gpu_forward(g, cam, bg, H, W, binning=binning)
     assert torch.equal(color, color2) and torch.equal(depth, depth2) and torch.equal(radii, radii2), "determinism"
 
 
