@@ -62,6 +62,7 @@ def parse_args():
     ap.add_argument("--config", default="C2", choices=sorted(CONFIGS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--eager", action="store_true", help="launch every step eagerly instead of replaying a CUDA graph")
     a = ap.parse_args()
     single = CONFIGS[a.config]["frames"] is None
     if a.steps is None:
@@ -254,8 +255,8 @@ class Workload:
                 lj = self.image_loss.apply(out["render"], self.dev[j]["gt"], wl1, -wss, wss)  # train.py:245-250
                 loss = lj if loss is None else loss + lj
             loss.backward()
-            self.last = out
             result = loss.detach()
+            del loss, out, d_xyz, d_rot, d_scale   # (nothing may keep the autograd graph alive across steps)
         else:
             with torch.no_grad():
                 result = torch.zeros((), device=self.device)
@@ -268,7 +269,6 @@ class Workload:
                     for i, j in enumerate(idx):
                         out = render(self.cams[j], g, self.pipe, self.bg, d_xyz[i], d_rot[i], d_scale[i], False)
                         result = result + out["render"][:, ::64, ::64].sum()   # a checksum that depends on every frame
-                self.last = out
         if from_host:
             # the result travels to pinned host memory every step; the host reads it when it next waits for this
             # step (timed_region keeps at most two steps in flight), like a training loop that logs one step late
@@ -281,6 +281,25 @@ class Workload:
     def exchange(self):
         if self.world > 1 and self.cfg["train"]:
             self.grads.all_reduce()
+
+    def enable_graphs(self):
+        """Capture step(False) and step(True) into CUDA graphs (frames.GraphedStep); later step() calls replay them.
+        The multi-GPU gradient exchange stays an eager NCCL call after the replay."""
+        frames = pkg("frames")
+        self._graphs = {}
+        eager = self.step
+        for from_host in (False, True):
+            self._graphs[from_host] = frames.GraphedStep(lambda fh=from_host: eager(fh), warmup=2,
+                                                         checks=[self.capacity.check, self.model.deform.check_status])
+        self._eager_step = eager
+
+        def replay(from_host):
+            g = self._graphs[from_host]
+            slot = g()
+            if from_host:
+                self.steps_done += 1
+            return slot
+        self.step = replay
 
 
 def timed_region(work, steps, from_host, world, dist):
@@ -337,8 +356,9 @@ def kernel_table(work, steps):
     n = lib.d3g_prof_count()
     torch.cuda.synchronize()
     lib.d3g_prof_enable(1)
+    step = getattr(work, "_eager_step", work.step)   # (the recorder brackets launches, so this pass runs eagerly)
     for _ in range(steps):
-        work.step(False)
+        step(False)
         work.exchange()
     ms = (C.c_double * n)()
     cnt = (C.c_int32 * n)()
@@ -609,6 +629,17 @@ def main():
     work = Workload(cfg, rank, world, device)
 
     warm = max(args.warmup, 3)
+    for _ in range(3):
+        work.step(False)
+        work.exchange()
+    graphed = False
+    if not args.eager and os.environ.get("D3G_BENCH_GRAPH", "1") == "1":
+        try:
+            work.enable_graphs()
+            graphed = True
+        except Exception as e:   # report and fall back to eager launches
+            print("bench.py: CUDA-graph capture failed (%s: %s); running eagerly" % (type(e).__name__, e), file=sys.stderr)
+            torch.cuda.synchronize()
     for _ in range(warm):
         work.step(False)
         work.exchange()
@@ -638,6 +669,9 @@ def main():
                        "loss": ("0.8*L1 + 0.2*(1-SSIM) vs fixed random images (fused CUDA loss); multi-frame batches use "
                                 "the reference's cumulative-L1 frame weights (train.py:245-250)") if cfg["train"] else None,
                        "pair_capacity": "GrowingPairCapacity: no num_rendered read-back inside a frame",
+                       "launch": ("one CUDA-graph replay per step (frames.GraphedStep: the whole fwd+bwd step incl. the "
+                                  "H2D/D2H copies of the end-to-end leg is captured once)" if graphed else
+                                  "eager: every kernel launched from Python each step"),
                        "l2": "per-step working set (saved MLP activation tiles, ~0.9 GB per 100k points) exceeds the 126 MB L2",
                        "parallelism": ("frame-parallel dp%d, one NCCL all-reduce of the flat gradient buffer, <= 2 steps in flight" % world)
                        if cfg["train"] else ("timestamp-parallel x%d, no collective" % world)},

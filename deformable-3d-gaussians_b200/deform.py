@@ -167,7 +167,7 @@ class _FusedDeform(torch.autograd.Function):
             gstruct = _fill_ptr_struct(_lib.MlpGrads(), [(n, g) for (n, _), g in zip(named, grads)])
             pstruct = _fill_ptr_struct(_lib.MlpParams(), named)
             cfg = net._cfg()
-            packed = net._packed(dev)
+            packed = net._packed(dev, reuse_in_capture=True)
             dxyz_in = torch.empty(rows, 3, dtype=torch.float32, device=dev) if ctx.xyz_requires_grad else None
             dt_in = None
             if ctx.t_requires_grad:
@@ -243,6 +243,7 @@ class _DeformBase(nn.Module):
         self.fused_grad_accumulation = False
         self._pack_cache = None
         self._status_pending, self._status_host, self._status_next = [], None, 0
+        self._graph_status, self._graph_pool = [], None   # pinned status slots of launches captured into CUDA graphs
 
     def _apply(self, fn, *a, **kw):
         self.__dict__.pop("_named_cache", None)
@@ -261,13 +262,18 @@ class _DeformBase(nn.Module):
         c.D, c.W, c.multires = int(self.D), int(self.W), int(self.multires)
         return c
 
-    def _packed(self, dev):
+    def _packed(self, dev, reuse_in_capture=False):
         """Packed weight images, rebuilt only when a parameter changed (tensor version counters)."""
         lib = _lib.load()
         named = _param_list(self)
         key = tuple((p.data_ptr(), p._version) for _, p in named) + (str(dev),)
-        if self._pack_cache is not None and self._pack_cache[0] == key:
+        capturing = torch.cuda.is_current_stream_capturing()
+        if capturing and reuse_in_capture and self._pack_cache is not None:
+            return self._pack_cache[1]         # backward of a forward captured (and packed) in the same graph
+        if not capturing and self._pack_cache is not None and self._pack_cache[0] == key:
             return self._pack_cache[1]
+        # (inside a CUDA-graph capture the pack kernel always becomes part of the graph: replays must see the
+        # parameter values of THEIR time, not those of capture time)
         cfg = self._cfg()
         nb = C.c_size_t()
         _lib.check(lib.d3g_mlp_packed_bytes(C.byref(cfg), C.byref(nb)))
@@ -287,9 +293,19 @@ class _DeformBase(nn.Module):
         memory on the stream right behind the launch and examined once that copy has completed — at the next
         call, or in check_status() — so a pipeline abort never goes unnoticed and the hot path never syncs.
         With debug set (D3G_DEBUG=1) the check is immediate."""
+        if torch.cuda.is_current_stream_capturing():
+            # the copy becomes a node of the graph; every replay refreshes the slot, check_status() reads it.
+            # (pinned memory cannot be allocated during a capture: the slots come from a pool made by an eager call)
+            if self._graph_pool is None or len(self._graph_status) >= self._graph_pool.numel():
+                raise RuntimeError("DeformNetwork: run the step eagerly once before capturing it into a CUDA graph")
+            slot = self._graph_pool[len(self._graph_status):len(self._graph_status) + 1]
+            slot.copy_(ws[:4].view(torch.int32), non_blocking=True)
+            self._graph_status.append(slot)
+            return
         self._poll_status(wait=len(self._status_pending) >= 32)
         if self._status_host is None:
             self._status_host = torch.zeros(64, dtype=torch.int32).pin_memory()
+            self._graph_pool = torch.zeros(256, dtype=torch.int32).pin_memory()
         i = self._status_next
         self._status_next = (i + 1) % 64
         slot = self._status_host[i:i + 1]
@@ -317,6 +333,12 @@ class _DeformBase(nn.Module):
     def check_status(self):
         """Wait for every launch issued so far and raise if one of them aborted."""
         self._poll_status(wait=True)
+        if self._graph_status:
+            torch.cuda.current_stream().synchronize()
+            for slot in self._graph_status:
+                if int(slot[0]) != 0:
+                    raise _lib.D3GError("fused MLP kernel (CUDA-graph replay) reported an internal pipeline timeout "
+                                        "(status %d); its outputs are invalid" % int(slot[0]))
 
     def read_activation_masks(self, ws, rows):
         """Parity hook: [8, rows, 256] bool activation pattern saved by the last training-mode forward."""

@@ -22,6 +22,49 @@ def frame_loss_weights(num_frames, lambda_dssim):
     return [((T - j) * (1.0 - lambda_dssim) / T, lambda_dssim / T) for j in range(T)]
 
 
+class GraphedStep:
+    """Capture one whole step of the path — DeformModel.step -> render -> loss -> backward, written against STATIC
+    tensors (parameters, camera tensors, ground truth, the flat gradient buffer) — into a CUDA graph and replay it.
+    A frame of this path is ~45 kernel launches issued from Python through five autograd Functions (~1.35 ms of
+    host time per frame, measured with a 2k-Gaussian frame) for ~1.6 ms of GPU work at 100k Gaussians, so an eager
+    loop is about to become launch-bound; a replay costs one launch.
+
+        step = GraphedStep(lambda: train_frame())      # runs fn a few times eagerly, then captures it
+        for it in ...:  upload_inputs(); out = step()  # out = whatever fn returned at capture (static tensors)
+
+    Requirements on fn: no host synchronisation (size the rasterizer's binning workspace with a
+    rasterizer.PAIR_CAPACITY_POLICY that has seen the shapes, e.g. GrowingPairCapacity after the warm-up calls), inputs
+    updated in place.  The deformation network re-packs its weights inside the graph, so parameter updates made
+    between replays (optimizer steps) are seen.  Status words / pair-count headers copied to pinned memory inside the
+    graph are examined by check() (call it where the host synchronises anyway)."""
+
+    def __init__(self, fn, warmup=3, checks=()):
+        self.fn, self.checks = fn, list(checks)
+        cur = torch.cuda.current_stream()
+        side = torch.cuda.Stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                fn()
+        cur.wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.out = fn()
+
+    def __call__(self):
+        self.graph.replay()
+        return self.out
+
+    def check(self):
+        for c in self.checks:
+            c()
+
+
+def capturing():
+    return torch.cuda.is_available() and torch.cuda.is_current_stream_capturing()
+
+
 class FlatGrads:
     """`params` in exchange order.  With `early` = the number of leading parameters whose gradients are
     complete early in backward (the Gaussian parameters: autograd accumulates them right after the rasterizer

@@ -55,13 +55,33 @@ class GrowingPairCapacity:
 
     def __init__(self, headroom=1.25):
         self.headroom, self.seen, self.pending, self.free = float(headroom), {}, [], []
+        self.graph_headers = []   # (key, cap, pinned header) of frames captured into CUDA graphs
+        self.graph_pool = None    # pinned slots for them (pinned memory cannot be allocated during a capture)
 
     def __call__(self, N, H, W):
+        if torch.cuda.is_current_stream_capturing():
+            r = self.seen.get((N, H, W))
+            if r is None:
+                raise RuntimeError("GrowingPairCapacity: shape (%d,%d,%d) must be rendered once before it is captured "
+                                   "into a CUDA graph" % (N, H, W))
+            return int(r * self.headroom) + 1024
         self._drain(block=False)
         r = self.seen.get((N, H, W))
         return None if r is None else int(r * self.headroom) + 1024
 
     def observe(self, key, cap, geom, lib):
+        if torch.cuda.is_current_stream_capturing():
+            # the header copy becomes a node of the graph; check() examines the slot after a replay has finished
+            n = len(self.graph_headers)
+            if self.graph_pool is None or 2 * n + 2 > self.graph_pool.numel():
+                raise RuntimeError("GrowingPairCapacity: render eagerly once before capturing into a CUDA graph")
+            host = self.graph_pool[2 * n:2 * n + 2]
+            _lib.check(lib.d3g_raster_header_async(_lib.ptr(geom), C.c_void_p(host.data_ptr()),
+                                                   C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+            self.graph_headers.append((key, cap, host))
+            return
+        if self.graph_pool is None:
+            self.graph_pool = torch.zeros(512, dtype=torch.int32).pin_memory()
         host = self.free.pop() if self.free else torch.zeros(2, dtype=torch.int32).pin_memory()
         stream = torch.cuda.current_stream()
         _lib.check(lib.d3g_raster_header_async(_lib.ptr(geom), C.c_void_p(host.data_ptr()), C.c_void_p(stream.cuda_stream)))
@@ -89,6 +109,13 @@ class GrowingPairCapacity:
 
     def check(self):
         bad = self._drain(block=True)
+        if self.graph_headers:
+            torch.cuda.current_stream().synchronize()
+            for key, cap, host in self.graph_headers:
+                R = int(host[0].item()) & 0xFFFFFFFF
+                if int(host[1].item()) != 0 or R > cap:
+                    raise RuntimeError("GaussianRasterizer: %d pairs exceeded the capacity %d baked into a CUDA graph "
+                                       "(N,H,W=%s); re-capture it with more headroom" % (R, cap, key))
         if bad is not None:
             raise RuntimeError("GaussianRasterizer: %d pairs exceeded the capacity %d of a sync-free frame (N,H,W=%s); "
                                "that frame's image is undefined — re-render it" % (bad[2], bad[1], bad[0]))
