@@ -172,8 +172,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
   uint64_t* empty = bars + kBwdNumStages;     // [kBwdNumStages]
   uint64_t* acc_full = bars + 2 * kBwdNumStages;
   uint64_t* dout_ready = acc_full + 1;
-  uint64_t* a_ready = dout_ready + 1;         // [8]
-  uint32_t* tmem_slot = (uint32_t*)(a_ready + 8);
+  // go[c]: chunk c of the next chain step may be multiplied = handed over by the four epilogue warps that produce it AND
+  // its weight stage has landed (same scheme as the forward kernel: one barrier poll per chunk on the issue thread)
+  uint64_t* go = dout_ready + 1;              // [8]
+  uint32_t* tmem_slot = (uint32_t*)(go + 8);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   volatile int* abort_flag = a.abort_flag;
@@ -182,7 +184,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
     for (int i = 0; i < kBwdNumStages; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     mbar_init(acc_full, 1);
     mbar_init(dout_ready, 8);
-    for (int i = 0; i < 8; i++) mbar_init(&a_ready[i], 4);
+    for (int i = 0; i < 8; i++) mbar_init(&go[i], 5);
     fence_barrier_init();
   }
   if (warp == 9) tmem_alloc(tmem_slot, 512);
@@ -203,8 +205,9 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
       for (int tile = blockIdx.x; ok && tile < a.tiles; tile += gridDim.x) {
         for (int st = 0; st < kBwdStages; st++) {
           if (!mbar_wait(&empty[s], ph ^ 1, abort_flag)) { ok = false; break; }
-          mbar_arrive_expect_tx(&full[s], kStageBytes);
-          bulk_g2s(sStage + (size_t)s * kStageBytes, a.wbwd + (size_t)st * kStageBytes, kStageBytes, &full[s]);
+          uint64_t* bar = st == 0 ? &full[s] : &go[(st - 1) & 7];   // stage 0 = heads^T, then 7 x 8 chunk stages
+          mbar_arrive_expect_tx(bar, kStageBytes);
+          bulk_g2s(sStage + (size_t)s * kStageBytes, a.wbwd + (size_t)st * kStageBytes, kStageBytes, bar);
           if (++s == kBwdNumStages) { s = 0; ph ^= 1; }
         }
       }
@@ -214,20 +217,22 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
     if (lane == 0) {
       const uint32_t idesc256 = make_idesc_f16(128, 256, 0, 0);
       int s = 0;
-      uint32_t ph = 0, d_ph = 0, a_ph = 0;
+      uint32_t ph = 0, d_ph = 0, a_ph = 0, full_bits = 0;   // (full[s] only completes for the heads^T stage: per-slot parity)
       bool ok = true;
+      const uint64_t bdesc0 = make_smem_desc(smem_u32(sStage), 16, 1024);
       auto release = [&]() { umma_commit(&empty[s]); if (++s == kBwdNumStages) { s = 0; ph ^= 1; } };
       for (int tile = blockIdx.x; ok && tile < a.tiles; tile += gridDim.x) {
         // step 0: dH_7 = dOut[128,16] * Wheads[16,256]  (A from shared memory, K = 16; W = hi + lo)
         if (!mbar_wait(dout_ready, d_ph, abort_flag)) { ok = false; break; }
         d_ph ^= 1;
-        if (!mbar_wait(&full[s], ph, abort_flag)) { ok = false; break; }
+        if (!mbar_wait(&full[s], (full_bits >> s) & 1u, abort_flag)) { ok = false; break; }
+        full_bits ^= 1u << s;
         tc_fence_after();
         {
-          const uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes);
+          const uint64_t sb = desc_adv(bdesc0, (uint32_t)s * kStageBytes);
           const uint64_t ad = make_smem_desc(smem_u32(sDout), 16, 1024);
-          umma_f16_ss(tmem_base + 0, ad, make_smem_desc(sb, 16, 1024), idesc256, 0u);
-          umma_f16_ss(tmem_base + 0, ad, make_smem_desc(sb + 64, 16, 1024), idesc256, 1u);
+          umma_f16_ss(tmem_base + 0, ad, sb, idesc256, 0u);
+          umma_f16_ss(tmem_base + 0, ad, desc_adv(sb, 64), idesc256, 1u);
           release();
           umma_commit(acc_full);
         }
@@ -235,15 +240,14 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
         for (int j = 1; ok && j < 8; j++) {
           const uint32_t d_col = (j & 1) * 256, a_col = ((j - 1) & 1) * 256;
           for (int kc = 0; ok && kc < 8; kc++) {
-            if (!mbar_wait(&a_ready[kc], a_ph, abort_flag)) { ok = false; break; }
-            if (!mbar_wait(&full[s], ph, abort_flag)) { ok = false; break; }
+            if (!mbar_wait(&go[kc], a_ph, abort_flag)) { ok = false; break; }
             tc_fence_after();
-            const uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes);
+            const uint64_t sb = desc_adv(bdesc0, (uint32_t)s * kStageBytes);
             const uint32_t ta = tmem_base + a_col + kc * 32;
 #pragma unroll
             for (int ks = 0; ks < 2; ks++) {
-              umma_f16_ts(tmem_base + d_col, ta + ks * 8, make_smem_desc(sb + ks * 32, 16, 1024), idesc256, (kc | ks) != 0);
-              umma_f16_ts(tmem_base + d_col, ta + ks * 8, make_smem_desc(sb + 64 + ks * 32, 16, 1024), idesc256, 1u);
+              umma_f16_ts(tmem_base + d_col, ta + ks * 8, desc_adv(sb, ks * 32), idesc256, (kc | ks) != 0);
+              umma_f16_ts(tmem_base + d_col, ta + ks * 8, desc_adv(sb, 64 + ks * 32), idesc256, 1u);
             }
             release();
           }
@@ -309,7 +313,12 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
 #pragma unroll
         for (int i = 0; i < 4; i++)
           mbits[i] = a.mask[(((size_t)l * a.tiles + tile) * 8 + (chalf + 2 * i)) * 128 + row];
-        if (!mbar_wait(acc_full, acc_ph, abort_flag)) { ok = false; break; }
+        {   // one lane polls, the warp follows
+          int got = 1;
+          if (lane == 0) got = mbar_wait(acc_full, acc_ph, abort_flag) ? 1 : 0;
+          got = __shfl_sync(0xffffffffu, got, 0);
+          if (!got) { ok = false; break; }
+        }
         acc_ph ^= 1;
         tc_fence_after();
         const uint32_t half = (j & 1) * 256;
@@ -333,7 +342,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
             tmem_wait_st();
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&a_ready[c]);
+            if (lane == 0) mbar_arrive(&go[c]);
           }
           // dZ -> [point][feature] image: 64 bytes = four 16-byte chunks of this thread's row inside panel c/2
           uint8_t* dst = a.dz_img + ((size_t)l * a.tiles + tile) * kHBytes + (size_t)(c >> 1) * kPanelBytes + row * 128;

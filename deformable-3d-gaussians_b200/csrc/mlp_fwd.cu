@@ -18,6 +18,7 @@
 // Warp roles (kEpiWarps = 8): 0-7 epilogue/PE (warp w owns TMEM lanes 32*(w&3).., column chunks of parity w>>2),
 // 8 weight producer, 9 MMA issuer + TMEM owner.
 #include <math.h>
+#include <stdlib.h>
 
 #include "mlp_common.cuh"
 
@@ -33,7 +34,7 @@ struct FwdSmem {
   static constexpr uint32_t stages = kPeSmemBytes;
   static constexpr uint32_t bias = stages + kNumStages * kStageBytes;
   static constexpr uint32_t bars = bias + kBiasFloats * 4 + 64;  // 8-byte aligned
-  static constexpr uint32_t total = bars + 256;
+  static constexpr uint32_t total = bars + 320;
 };
 static_assert(FwdSmem::bars % 8 == 0, "barrier alignment");
 
@@ -58,7 +59,14 @@ struct MlpFwdArgs {
   float* d_rot;
   float* d_scale;
   int* abort_flag;
+  int dbg;   // timing experiments only (D3G_FWD_DBG): bit0 skip tcgen05.st, bit1 skip tcgen05.ld, bit3 1/8 weight bytes,
+             // bit4 one product instead of three, bit5 clock stamps of CTA 0's second tile into status[16..]
+  int* tl;   // timeline buffer (status + 16), 224 ints
 };
+#define TL(slot)                                                                                     \
+  do {                                                                                               \
+    if ((a.dbg & 32) && blockIdx.x == 0 && tile == (int)gridDim.x) a.tl[slot] = (int)(clock64() - tl0); \
+  } while (0)
 
 __device__ __forceinline__ void stg128(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
@@ -75,8 +83,17 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
   uint64_t* empty = bars + kNumStages;     // [kNumStages]
   uint64_t* acc_full = bars + 2 * kNumStages;
   uint64_t* pe_ready = acc_full + 1;
-  uint64_t* a_ready = pe_ready + 1;        // [8]
-  uint32_t* tmem_slot = (uint32_t*)(a_ready + 8);
+  // go[c]: "chunk c (32 features) of the next layer may be multiplied" = its A operand has been handed over by the four
+  // epilogue warps that produce it AND its weight stage has landed (the producer's expect_tx lands on the same
+  // barrier).  One wait per chunk on the issuing thread instead of two: an mbarrier poll costs that thread ~200 clk
+  // and it shares its scheduler with two epilogue warps (measured 1250 clk per chunk against 810 clk of tensor work
+  // while the epilogue runs).
+  uint64_t* go = pe_ready + 1;             // [8]
+  // The heads step has its own hand-over barriers (8 epilogue warps only; its single weight stage is waited for
+  // through full[s]): the producer runs up to kNumStages stages ahead, i.e. into the NEXT tile's layer-1 stages while
+  // layer 7's epilogue is still handing over, so those arrivals must not meet the heads phase on go[].
+  uint64_t* goh = go + 8;                  // [8]
+  uint32_t* tmem_slot = (uint32_t*)(goh + 8);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   volatile int* abort_flag = a.abort_flag;
@@ -85,7 +102,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
     for (int i = 0; i < kNumStages; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     mbar_init(acc_full, 1);
     mbar_init(pe_ready, 8);
-    for (int i = 0; i < 8; i++) mbar_init(&a_ready[i], 4);
+    for (int i = 0; i < 8; i++) { mbar_init(&go[i], 5); mbar_init(&goh[i], 4); }   // 4 epilogue warps (+ 1 weight stage)
     fence_barrier_init();
   }
   if (warp == kEpiWarps + 1) tmem_alloc(tmem_slot, 512);
@@ -94,6 +111,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const long long tl0 = clock64();
 
   if (warp == kEpiWarps) {
     // ================= weight producer =================
@@ -104,9 +122,17 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
       for (int tile = blockIdx.x; ok && tile < a.tiles; tile += gridDim.x) {
         for (int st = 0; st < kFwdStages; st++) {
           if (!mbar_wait(&empty[s], ph ^ 1, abort_flag)) { ok = false; break; }
-          uint32_t bytes = st == kFwdStages - 1 ? 16384u : kStageBytes;
-          mbar_arrive_expect_tx(&full[s], bytes);
-          bulk_g2s(sStage + (size_t)s * kStageBytes, a.wfwd + (size_t)st * kStageBytes, bytes, &full[s]);
+          int layer, kp;
+          fwd_stage_info(st, layer, kp);
+          uint64_t* bar = &full[s];                       // pe-fed stages (layer 0, pe part of layer 5)
+          uint32_t bytes = kStageBytes;
+          if (layer == 9) {                               // heads: one 16 KB stage, waited for through full[s]
+            bytes = 16384u;
+          } else if (layer != 0 && layer != 8) {
+            bar = &go[kp];
+          }
+          mbar_arrive_expect_tx(bar, bytes);
+          bulk_g2s(sStage + (size_t)s * kStageBytes, a.wfwd + (size_t)st * kStageBytes, bytes, bar);
           if (++s == kNumStages) { s = 0; ph ^= 1; }
         }
       }
@@ -119,9 +145,18 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
       const uint32_t idesc256 = make_idesc_f16(128, 256, 0, 0);
       const uint32_t idesc16 = make_idesc_f16(128, 16, 0, 0);
       int s = 0;
-      uint32_t ph = 0, pe_ph = 0, a_ph = 0;
+      uint32_t ph = 0, pe_ph = 0, a_ph = 0, h_ph = 0;
       bool ok = true;
-      auto wait_full = [&]() { return mbar_wait(&full[s], ph, abort_flag); };
+      // (this thread shares its scheduler with two epilogue warps: everything it executes per MMA counts — descriptors
+      // are advanced from two precomputed bases, barrier waits are non-suspending polls)
+      const uint64_t bdesc0 = make_smem_desc(smem_u32(sStage), 16, 1024), adesc0 = make_smem_desc(smem_u32(sPE), 16, 1024);
+      // full[s] only completes for the pe-fed stages that pass through slot s: its parity is tracked per slot
+      uint32_t full_bits = 0;
+      auto wait_full = [&]() {
+        const bool r = mbar_wait(&full[s], (full_bits >> s) & 1u, abort_flag);
+        full_bits ^= 1u << s;
+        return r;
+      };
       auto release = [&]() { umma_commit(&empty[s]); if (++s == kNumStages) { s = 0; ph ^= 1; } };
       for (int tile = blockIdx.x; ok && tile < a.tiles; tile += gridDim.x) {
         if (!mbar_wait(pe_ready, pe_ph, abort_flag)) { ok = false; break; }
@@ -132,19 +167,16 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
           for (int kc = 0; ok && kc < 3; kc++) {
             if (!wait_full()) { ok = false; break; }
             tc_fence_after();
-            const uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes);
-            const uint32_t sa = smem_u32(sPE) + kc * kPanelBytes;
+            const uint64_t sb = desc_adv(bdesc0, (uint32_t)s * kStageBytes);
+            const uint64_t sa = desc_adv(adesc0, (uint32_t)kc * kPanelBytes);
 #pragma unroll
             for (int ks = 0; ks < 2; ks++) {   // hi * Whi
-              umma_f16_ss(tmem_base + d_col, make_smem_desc(sa + ks * 32, 16, 1024),
-                          make_smem_desc(sb + ks * 32, 16, 1024), idesc256, (kc | ks) != 0);
+              umma_f16_ss(tmem_base + d_col, desc_adv(sa, ks * 32), desc_adv(sb, ks * 32), idesc256, (kc | ks) != 0);
             }
 #pragma unroll
             for (int ks = 0; ks < 2; ks++) {   // lo * Whi, hi * Wlo
-              umma_f16_ss(tmem_base + d_col, make_smem_desc(sa + 64 + ks * 32, 16, 1024),
-                          make_smem_desc(sb + ks * 32, 16, 1024), idesc256, 1u);
-              umma_f16_ss(tmem_base + d_col, make_smem_desc(sa + ks * 32, 16, 1024),
-                          make_smem_desc(sb + 64 + ks * 32, 16, 1024), idesc256, 1u);
+              umma_f16_ss(tmem_base + d_col, desc_adv(sa, 64 + ks * 32), desc_adv(sb, ks * 32), idesc256, 1u);
+              umma_f16_ss(tmem_base + d_col, desc_adv(sa, ks * 32), desc_adv(sb, 64 + ks * 32), idesc256, 1u);
             }
             release();
           }
@@ -152,27 +184,31 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
         // h-fed part: A from tensor memory, handed over 32 features at a time
         auto h_part = [&](uint32_t d_col, uint32_t a_col, bool accumulate_first) {
           for (int kc = 0; ok && kc < 8; kc++) {
-            if (!mbar_wait(&a_ready[kc], a_ph, abort_flag)) { ok = false; break; }
-            if (!wait_full()) { ok = false; break; }
+            if (!mbar_wait(&go[kc], a_ph, abort_flag)) { ok = false; break; }
             tc_fence_after();
-            const uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes);
+            if (d_col == 256 && a_col == 0) TL(16 + kc);          // odd layers: chunk kc may be multiplied
+            const uint64_t sb = desc_adv(bdesc0, (uint32_t)s * kStageBytes);
             const uint32_t ta = tmem_base + a_col + kc * 32;
 #pragma unroll
             for (int ks = 0; ks < 2; ks++)
-              umma_f16_ts(tmem_base + d_col, ta + ks * 8, make_smem_desc(sb + ks * 32, 16, 1024), idesc256,
+              umma_f16_ts(tmem_base + d_col, ta + ks * 8, desc_adv(sb, ks * 32), idesc256,
                           (accumulate_first || (kc | ks) != 0) ? 1u : 0u);
+            if (!(a.dbg & 16)) {
 #pragma unroll
             for (int ks = 0; ks < 2; ks++) {
-              umma_f16_ts(tmem_base + d_col, ta + 16 + ks * 8, make_smem_desc(sb + ks * 32, 16, 1024), idesc256, 1u);
-              umma_f16_ts(tmem_base + d_col, ta + ks * 8, make_smem_desc(sb + 64 + ks * 32, 16, 1024), idesc256, 1u);
+              umma_f16_ts(tmem_base + d_col, ta + 16 + ks * 8, desc_adv(sb, ks * 32), idesc256, 1u);
+              umma_f16_ts(tmem_base + d_col, ta + ks * 8, desc_adv(sb, 64 + ks * 32), idesc256, 1u);
+            }
             }
             release();
           }
           a_ph ^= 1;
         };
+        TL(0);
         pe_part(0);                       // layer 0 -> half 0
         if (!ok) break;
         umma_commit(acc_full);
+        TL(1);
         for (int l = 1; ok && l < 8; l++) {
           uint32_t d_col = (l & 1) * 256, a_col = ((l - 1) & 1) * 256;
           if (l == 5) {
@@ -184,28 +220,28 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
           }
           if (!ok) break;
           umma_commit(acc_full);
+          TL(1 + l);
         }
         if (!ok) break;
         // heads: N = 16, A = h7 (half 1), D = half 0 columns 0..15, single 16 KB stage of 8 chunks x 2 KB
         {
-          bool have = false;
+          if (!wait_full()) { ok = false; break; }
           for (int kc = 0; ok && kc < 8; kc++) {
-            if (!mbar_wait(&a_ready[kc], a_ph, abort_flag)) { ok = false; break; }
-            if (!have) { if (!wait_full()) { ok = false; break; } have = true; }
+            if (!mbar_wait(&goh[kc], h_ph, abort_flag)) { ok = false; break; }
             tc_fence_after();
-            const uint32_t sb = smem_u32(sStage + (size_t)s * kStageBytes) + kc * 2048;
+            const uint64_t sb = desc_adv(bdesc0, (uint32_t)s * kStageBytes + (uint32_t)kc * 2048u);
             const uint32_t ta = tmem_base + 256 + kc * 32;
 #pragma unroll
             for (int ks = 0; ks < 2; ks++)
-              umma_f16_ts(tmem_base + 0, ta + ks * 8, make_smem_desc(sb + ks * 32, 16, 1024), idesc16, (kc | ks) != 0);
+              umma_f16_ts(tmem_base + 0, ta + ks * 8, desc_adv(sb, ks * 32), idesc16, (kc | ks) != 0);
 #pragma unroll
             for (int ks = 0; ks < 2; ks++) {
-              umma_f16_ts(tmem_base + 0, ta + 16 + ks * 8, make_smem_desc(sb + ks * 32, 16, 1024), idesc16, 1u);
-              umma_f16_ts(tmem_base + 0, ta + ks * 8, make_smem_desc(sb + 64 + ks * 32, 16, 1024), idesc16, 1u);
+              umma_f16_ts(tmem_base + 0, ta + 16 + ks * 8, desc_adv(sb, ks * 32), idesc16, 1u);
+              umma_f16_ts(tmem_base + 0, ta + ks * 8, desc_adv(sb, 64 + ks * 32), idesc16, 1u);
             }
           }
           if (!ok) break;
-          a_ph ^= 1;
+          h_ph ^= 1;
           release();
           umma_commit(acc_full);
         }
@@ -288,15 +324,27 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
 
       // ---- trunk epilogues: bias + ReLU + hi/lo split in place in TMEM, 32 features at a time ----
       for (int l = 0; ok && l < 8; l++) {
-        if (!mbar_wait(acc_full, acc_ph, abort_flag)) { ok = false; break; }
+        {   // one lane polls, the warp follows: 8 pollers instead of 256 on the barrier word
+          int got = 1;
+          if (lane == 0) got = mbar_wait(acc_full, acc_ph, abort_flag) ? 1 : 0;
+          got = __shfl_sync(0xffffffffu, got, 0);
+          if (!got) { ok = false; break; }
+        }
         acc_ph ^= 1;
         tc_fence_after();
+        if (lane == 0 && q == 0 && l < 3) TL(40 + l * 24 + cg * 12);
         const uint32_t half = (l & 1) * 256;
         const float* bl = sBias + l * 256;
         for (int c = cg; c < 8; c += kEpiWarps / 4) {
           uint32_t v[32];
-          tmem_ld32(lane_addr + half + c * 32, v);
-          tmem_wait_ld();
+          if (!(a.dbg & 2)) {
+            tmem_ld32(lane_addr + half + c * 32, v);
+            tmem_wait_ld();
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; j++) v[j] = 0x3f000000u + j;
+          }
+          if (lane == 0 && q == 0 && l < 3) TL(40 + l * 24 + cg * 12 + 1 + (c >> 1) * 2);
           uint32_t bits = 0;
           float bv[32];
           const uint32_t bl_s = smem_u32(bl + c * 32);
@@ -322,12 +370,13 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
             }
             split2(r[0], r[1], o[j >> 1], o[16 + (j >> 1)]);
           }
-          tmem_st32(lane_addr + half + c * 32, o);
+          if (!(a.dbg & 1)) tmem_st32(lane_addr + half + c * 32, o);
           // hand the chunk to the MMA warp first, then save it for backward
           tmem_wait_st();
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&a_ready[c]);
+          if (lane == 0) mbar_arrive(l == 7 ? &goh[c] : &go[c]);
+          if (lane == 0 && q == 0 && l < 3) TL(40 + l * 24 + cg * 12 + 1 + (c >> 1) * 2 + 1);
           if (a.save) {
             // hi part -> [point][feature] image: this thread's 32 features are 64 bytes = four 16-byte chunks of
             // its row inside panel c/2
@@ -720,6 +769,8 @@ static int mlp_forward_impl(const d3g_mlp_config* cfg, const void* packed, const
   a.pe_img = ws.pe_img; a.h_img = ws.h_img; a.mask = ws.mask; a.heads_out = ws.heads_out;
   a.d_xyz = d_xyz; a.d_rot = (cfg->heads & 2) ? d_rot : nullptr; a.d_scale = (cfg->heads & 4) ? d_scale : nullptr;
   a.abort_flag = ws.status;
+  { const char* e = getenv("D3G_FWD_DBG"); a.dbg = e ? atoi(e) : 0; }
+  a.tl = ws.status + 16;
   size_t smem = FwdSmem::total + 1024;
   D3G_CUDA_TRY(cudaFuncSetAttribute(mlp_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = a.tiles < num_sms() ? a.tiles : num_sms();

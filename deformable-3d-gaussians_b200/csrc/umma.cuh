@@ -75,6 +75,28 @@ __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, volati
   return false;
 }
 
+// Non-suspending variant for the single MMA-issuing thread: mbarrier.test_wait returns at once (try_wait may park the
+// thread; measured ~180 clk per call even on a completed phase, twice per 32-feature chunk on the issue thread).
+__device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ bool mbar_wait_spin(uint64_t* bar, uint32_t parity, volatile int* abort_flag) {
+  for (uint32_t spin = 0; spin < (1u << 24); spin++) {
+    if (mbar_test_wait(bar, parity)) return true;
+    if ((spin & 4095u) == 4095u && *abort_flag) return false;
+  }
+  *abort_flag = 1;
+  return false;
+}
+
 // make generic-proxy writes to shared memory visible to the async proxy (bulk copies, tcgen05.mma)
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -130,6 +152,9 @@ __device__ __forceinline__ uint64_t make_smem_desc_t(uint32_t saddr, uint32_t lb
 __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
   return make_smem_desc_t(saddr, lbo_bytes, sbo_bytes, 2u);
 }
+// advance the start address of a descriptor by `bytes` (a multiple of 16; shared-memory addresses stay below 2^18, so
+// the 14-bit field never carries)
+__device__ __forceinline__ uint64_t desc_adv(uint64_t d, uint32_t bytes) { return d + (uint64_t)(bytes >> 4); }
 // MN-major wgrad image operand: start of a group of 8 points inside a 32-point chunk
 __device__ __forceinline__ uint64_t make_smem_desc_mn(uint32_t saddr) {
   return make_smem_desc_t(saddr, 4096u, 512u, 1u);
