@@ -36,7 +36,8 @@ constexpr int kBwdThreads = 320;
 struct BwdSmem {
   static constexpr uint32_t dout = 0;                       // 16 KB K-major panel (64 columns, 16 used)
   static constexpr uint32_t stages = kPanelBytes;
-  static constexpr uint32_t headb = stages + kBwdNumStages * kStageBytes;  // 16 floats
+  static constexpr uint32_t store = stages + kBwdNumStages * kStageBytes;  // [4 lane quarters][2] x 4 KB bulk-store staging
+  static constexpr uint32_t headb = store + 8 * 4096;                      // 16 floats
   static constexpr uint32_t bars = headb + 64;
   static constexpr uint32_t total = bars + 256;
 };
@@ -167,6 +168,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
   uint8_t* sDout = smem + BwdSmem::dout;
   uint8_t* sStage = smem + BwdSmem::stages;
   float* sHeadB = (float*)(smem + BwdSmem::headb);
+  uint8_t* sStore = smem + BwdSmem::store;
   uint64_t* bars = (uint64_t*)(smem + BwdSmem::bars);
   uint64_t* full = bars;                      // [kBwdNumStages]
   uint64_t* empty = bars + kBwdNumStages;     // [kBwdNumStages]
@@ -344,15 +346,29 @@ __global__ void __launch_bounds__(kBwdThreads, 1) mlp_dgrad_kernel(MlpBwdArgs a)
             __syncwarp();
             if (lane == 0) mbar_arrive(&go[c]);
           }
-          // dZ -> [point][feature] image: 64 bytes = four 16-byte chunks of this thread's row inside panel c/2
-          uint8_t* dst = a.dz_img + ((size_t)l * a.tiles + tile) * kHBytes + (size_t)(c >> 1) * kPanelBytes + row * 128;
+          // dZ -> [point][feature] image: the two warps of a lane quarter assemble the 4 KB block (32 rows of panel
+          // c/2) in shared memory and the bulk-copy engine stores it (see the forward kernel)
+          {
+            const int pr = c >> 1;
+            uint8_t* stg = sStore + ((q * 2 + (pr & 1)) << 12);
+            if (chalf == 0 && lane == 0) bulk_wait_read<1>();
+            asm volatile("bar.sync %0, %1;" ::"r"(1 + q), "r"(64) : "memory");
+            const uint32_t line = smem_u32(stg) + lane * 128;
 #pragma unroll
-          for (int g = 0; g < 4; g++)
-            stg128b(dst + (((4 * (c & 1) + g) ^ (row & 7)) << 4), o[4 * g], o[4 * g + 1], o[4 * g + 2], o[4 * g + 3]);
+            for (int g = 0; g < 4; g++)
+              sts128(line + (((4 * (c & 1) + g) ^ (lane & 7)) << 4), o[4 * g], o[4 * g + 1], o[4 * g + 2], o[4 * g + 3]);
+            fence_proxy_async();
+            asm volatile("bar.sync %0, %1;" ::"r"(1 + q), "r"(64) : "memory");
+            if (chalf == 0 && lane == 0) {
+              bulk_s2g(a.dz_img + ((size_t)l * a.tiles + tile) * kHBytes + (size_t)pr * kPanelBytes + (size_t)q * 4096, stg, 4096);
+              bulk_commit();
+            }
+          }
         }
       }
       tc_fence_before();
     }
+    if (chalf == 0 && lane == 0) bulk_wait_all<0>();
   }
   tc_fence_before();
   __syncthreads();

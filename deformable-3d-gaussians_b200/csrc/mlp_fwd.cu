@@ -24,7 +24,7 @@
 
 namespace d3g {
 
-constexpr int kNumStages = 5;
+constexpr int kNumStages = 4;
 constexpr int kEpiWarps = 8;                        // 2 per TMEM lane quarter, 4 column chunks each per layer
 constexpr int kFwdThreads = (kEpiWarps + 2) * 32;   // + weight producer + MMA issuer
 
@@ -32,7 +32,8 @@ struct FwdSmem {
   // offsets inside dynamic shared memory (after 1024-alignment)
   static constexpr uint32_t pe = 0;
   static constexpr uint32_t stages = kPeSmemBytes;
-  static constexpr uint32_t bias = stages + kNumStages * kStageBytes;
+  static constexpr uint32_t store = stages + kNumStages * kStageBytes;   // [4 lane quarters][2] x 4 KB bulk-store staging
+  static constexpr uint32_t bias = store + 8 * 4096;
   static constexpr uint32_t bars = bias + kBiasFloats * 4 + 64;  // 8-byte aligned
   static constexpr uint32_t total = bars + 320;
 };
@@ -68,6 +69,9 @@ struct MlpFwdArgs {
     if ((a.dbg & 32) && blockIdx.x == 0 && tile == (int)gridDim.x) a.tl[slot] = (int)(clock64() - tl0); \
   } while (0)
 
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
 __device__ __forceinline__ void stg128(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
@@ -78,6 +82,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
   uint8_t* sPE = smem + FwdSmem::pe;
   uint8_t* sStage = smem + FwdSmem::stages;
   float* sBias = (float*)(smem + FwdSmem::bias);
+  uint8_t* sStore = smem + FwdSmem::store;
   uint64_t* bars = (uint64_t*)(smem + FwdSmem::bars);
   uint64_t* full = bars;                   // [kNumStages]
   uint64_t* empty = bars + kNumStages;     // [kNumStages]
@@ -378,12 +383,24 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
           if (lane == 0) mbar_arrive(l == 7 ? &goh[c] : &go[c]);
           if (lane == 0 && q == 0 && l < 3) TL(40 + l * 24 + cg * 12 + 1 + (c >> 1) * 2 + 1);
           if (a.save) {
-            // hi part -> [point][feature] image: this thread's 32 features are 64 bytes = four 16-byte chunks of
-            // its row inside panel c/2
-            uint8_t* dst = a.h_img + ((size_t)l * a.tiles + tile) * kHBytes + (size_t)(c >> 1) * kPanelBytes + row * 128;
+            // hi part -> [point][feature] image.  The two warps of a lane quarter hold the two 64-byte halves of the
+            // same 32 rows of panel c/2 = one contiguous 4 KB block of the image: they assemble it in shared memory and
+            // the bulk-copy engine writes it as one store (per-thread 16-byte global stores at a 128-byte lane stride
+            // stalled the epilogue: 8.5k instead of 3.3k clk per layer, profiles/r2_mlp_fwd_timeline.txt).
+            const int pr = c >> 1;
+            uint8_t* stg = sStore + ((q * 2 + (pr & 1)) << 12);
+            if (cg == 0 && lane == 0) bulk_wait_read<1>();     // the store issued from this buffer two pairs ago has left it
+            named_bar_sync(1 + q, 64);
+            const uint32_t line = smem_u32(stg) + lane * 128;
 #pragma unroll
             for (int g = 0; g < 4; g++)
-              stg128(dst + (((4 * (c & 1) + g) ^ (row & 7)) << 4), o[4 * g], o[4 * g + 1], o[4 * g + 2], o[4 * g + 3]);
+              sts128(line + (((4 * (c & 1) + g) ^ (lane & 7)) << 4), o[4 * g], o[4 * g + 1], o[4 * g + 2], o[4 * g + 3]);
+            fence_proxy_async();
+            named_bar_sync(1 + q, 64);
+            if (cg == 0 && lane == 0) {
+              bulk_s2g(a.h_img + ((size_t)l * a.tiles + tile) * kHBytes + (size_t)pr * kPanelBytes + (size_t)q * 4096, stg, 4096);
+              bulk_commit();
+            }
             a.mask[(((size_t)l * a.tiles + tile) * 8 + c) * 128 + row] = bits;
           }
         }
@@ -448,6 +465,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) mlp_fwd_kernel(MlpFwdArgs a) {
       }
       tc_fence_before();
     }
+    if (cg == 0 && lane == 0) bulk_wait_all<0>();
   }
   tc_fence_before();
   __syncthreads();
