@@ -186,8 +186,14 @@ class Workload:
         if cfg["train"]:
             # flat gradient buffer: parameter .grad tensors are views into it, so the multi-GPU exchange is
             # one all-reduce with no packing kernel
+            # world > 1: the Gaussian-parameter slice (92 % of the buffer) is all-reduced from inside backward, as soon as
+            # the rasterizer's backward has accumulated it, and overlaps the MLP backward; the persistent MLP kernels
+            # leave D3G_BENCH_SM_RESERVE SMs to the NCCL kernel (they otherwise own every SM and NCCL waits for them)
+            self.early = world > 1 and os.environ.get("D3G_BENCH_EARLY", "1") == "1"
             self.grads = frames.FlatGrads(g.parameters() + list(self.model.deform.parameters()),
-                                          early=len(g.parameters()) if (world > 1 and os.environ.get("D3G_BENCH_EARLY", "0") == "1") else 0)
+                                          early=len(g.parameters()) if self.early else 0)
+            if self.early:
+                pkg("_lib").load().d3g_mlp_sm_reserve(int(os.environ.get("D3G_BENCH_SM_RESERVE", "8")))
             self.grads.frames_per_reduce = max(len(self.mine), 1)
             self.flat = self.grads.flat
             # MLP backward adds straight into those .grad views (no per-parameter zero-fill + AccumulateGrad add)
@@ -287,11 +293,21 @@ class Workload:
         The multi-GPU gradient exchange stays an eager NCCL call after the replay."""
         frames = pkg("frames")
         self._graphs = {}
-        eager = self.step
+        eager, eager_exchange = self.step, self.exchange
+        in_graph = self.world > 1 and self.cfg["train"] and os.environ.get("D3G_BENCH_NCCL_IN_GRAPH", "1") == "1"
+
+        def both(fh):
+            slot = eager(fh)
+            eager_exchange()
+            return slot
         for from_host in (False, True):
-            self._graphs[from_host] = frames.GraphedStep(lambda fh=from_host: eager(fh), warmup=2,
+            fn = (lambda fh=from_host: both(fh)) if in_graph else (lambda fh=from_host: eager(fh))
+            self._graphs[from_host] = frames.GraphedStep(fn, warmup=2,
                                                          checks=[self.capacity.check, self.model.deform.check_status])
         self._eager_step = eager
+        self.collective_in_graph = in_graph
+        if in_graph:
+            self.exchange = lambda: None     # the all-reduces are nodes of the step graph
 
         def replay(from_host):
             g = self._graphs[from_host]
@@ -357,9 +373,10 @@ def kernel_table(work, steps):
     torch.cuda.synchronize()
     lib.d3g_prof_enable(1)
     step = getattr(work, "_eager_step", work.step)   # (the recorder brackets launches, so this pass runs eagerly)
+    exchange = work.grads.all_reduce if (work.world > 1 and work.cfg["train"]) else (lambda: None)
     for _ in range(steps):
         step(False)
-        work.exchange()
+        exchange()
     ms = (C.c_double * n)()
     cnt = (C.c_int32 * n)()
     pkg("_lib").check(lib.d3g_prof_collect(ms, cnt, n))
@@ -673,7 +690,10 @@ def main():
                                   "H2D/D2H copies of the end-to-end leg is captured once)" if graphed else
                                   "eager: every kernel launched from Python each step"),
                        "l2": "per-step working set (saved MLP activation tiles, ~0.9 GB per 100k points) exceeds the 126 MB L2",
-                       "parallelism": ("frame-parallel dp%d, one NCCL all-reduce of the flat gradient buffer, <= 2 steps in flight" % world)
+                       "parallelism": ("frame-parallel dp%d, NCCL all-reduce of the flat gradient buffer (Gaussian slice issued "
+                                       "from inside backward, overlapping the MLP backward on reserved SMs: %s; collectives "
+                                       "captured in the step graph: %s), <= 2 steps in flight" %
+                                       (world, getattr(work, "early", False), getattr(work, "collective_in_graph", False)))
                        if cfg["train"] else ("timestamp-parallel x%d, no collective" % world)},
             "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": work.h2d_bytes, "d2h_bytes_per_step": 4,
                     "ms_per_step": sec_e2e / args.steps * 1e3, "results_read": len(work.losses),
@@ -709,7 +729,18 @@ def main():
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
+        # tear down: graphs that captured NCCL kernels must go before the communicator; a watchdog ends the process if
+        # the teardown itself blocks (the result line is already out)
+        threading.Timer(20.0, lambda: os._exit(0)).start()
+        torch.cuda.synchronize()
+        dist.barrier()
+        if hasattr(work, "_graphs"):
+            work._graphs.clear()
+            import gc
+            gc.collect()
+        torch.cuda.synchronize()
         dist.destroy_process_group()
+        os._exit(0)
 
 
 if __name__ == "__main__":

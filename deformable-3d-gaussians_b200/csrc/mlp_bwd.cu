@@ -1047,7 +1047,7 @@ static int mlp_backward_impl(const d3g_mlp_config* cfg, const void* packed, cons
       D3G_LAUNCH_CHECK(0, stream); }
     size_t smem = BwdSmem::total + 1024;
     D3G_CUDA_TRY(cudaFuncSetAttribute(mlp_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int grid = tiles < num_sms() ? tiles : num_sms();
+    int grid = tiles < mlp_grid_limit() ? tiles : mlp_grid_limit();
     { ProfScope _p(PROF_MLP_DGRAD, stream);
     mlp_dgrad_kernel<<<grid, kBwdThreads, smem, stream>>>(a);
     D3G_LAUNCH_CHECK(0, stream); }
@@ -1087,7 +1087,7 @@ static int mlp_backward_impl(const d3g_mlp_config* cfg, const void* packed, cons
     for (int j = 0; j < 16; j++) a.head_dw[j] = hm.w[j] ? (float*)hm.w[j] + (size_t)hm.r[j] * 256 : nullptr;
     size_t smem = (size_t)kWgStages * kWgStageBytes + 256 + 1024;
     D3G_CUDA_TRY(cudaFuncSetAttribute(mlp_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int grid = num_sms();
+    int grid = mlp_grid_limit();
     { ProfScope _p(PROF_MLP_WGRAD, stream);
     mlp_wgrad_kernel<<<grid, kWgThreads, smem, stream>>>(a);
     D3G_LAUNCH_CHECK(0, stream); }

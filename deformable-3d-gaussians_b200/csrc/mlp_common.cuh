@@ -199,5 +199,6 @@ inline HeadMap head_map(const d3g_mlp_config& cfg, const d3g_mlp_params& p) {
 
 int check_cfg(const d3g_mlp_config* cfg);
 int num_sms();
+int mlp_grid_limit();   // num_sms() minus the SMs reserved for a concurrent collective
 
 }  // namespace d3g

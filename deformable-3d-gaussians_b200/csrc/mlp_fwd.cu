@@ -688,6 +688,11 @@ int check_cfg(const d3g_mlp_config* cfg) {
   return 0;
 }
 
+static int g_sm_reserve = 0;     // SMs the persistent MLP kernels leave free (d3g_mlp_sm_reserve)
+int mlp_grid_limit() {
+  const int n = num_sms() - g_sm_reserve;
+  return n < 1 ? 1 : n;
+}
 static int g_num_sms[64] = {};   // per device
 int num_sms() {
   int dev = 0;
@@ -791,7 +796,7 @@ static int mlp_forward_impl(const d3g_mlp_config* cfg, const void* packed, const
   a.tl = ws.status + 16;
   size_t smem = FwdSmem::total + 1024;
   D3G_CUDA_TRY(cudaFuncSetAttribute(mlp_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int grid = a.tiles < num_sms() ? a.tiles : num_sms();
+  int grid = a.tiles < mlp_grid_limit() ? a.tiles : mlp_grid_limit();
   { ProfScope _p(PROF_MLP_FWD, stream);
     mlp_fwd_kernel<<<grid, kFwdThreads, smem, stream>>>(a);
   D3G_LAUNCH_CHECK(0, stream); }
@@ -811,6 +816,12 @@ int d3g_mlp_forward_times(const d3g_mlp_config* cfg, const void* packed, const d
   if (n_times < 1) return set_err(D3G_ERR_INVALID, "n_times must be >= 1");
   return mlp_forward_impl(cfg, packed, p, n_points, n_times, xyz, t_values, 0, workspace, save, d_xyz, d_rot,
                           d_scale, (cudaStream_t)stream_);
+}
+
+int d3g_mlp_sm_reserve(int32_t n_sms) {
+  if (n_sms < 0 || n_sms > 64) return set_err(D3G_ERR_INVALID, "sm reserve must be in [0, 64]");
+  g_sm_reserve = n_sms;
+  return 0;
 }
 
 int d3g_mlp_read_status(const void* workspace, int32_t* status_host, void* stream_) {

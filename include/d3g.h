@@ -304,6 +304,11 @@ int d3g_mlp_backward_times(const d3g_mlp_config* cfg, const void* packed, const 
                            const float* dL_dscale, const d3g_mlp_grads* g, float* dL_dxyz, float* dL_dt,
                            void* stream);
 
+/* The MLP kernels are persistent (one CTA per SM, all of its shared memory).  A collective that should overlap them —
+ * the all-reduce of the Gaussian-parameter gradients, which are complete before the MLP backward starts — needs SMs
+ * of its own: n_sms > 0 makes the forward / dgrad / wgrad grids leave that many SMs free.  Process-wide; 0 = default. */
+int d3g_mlp_sm_reserve(int32_t n_sms);
+
 /* Synchronises `stream` and returns the kernels' status word (0 = ok, non-zero = an internal
  * pipeline wait timed out, i.e. a bug).  Tests and debug mode call it; the hot path does not. */
 int d3g_mlp_read_status(const void* workspace, int32_t* status_host, void* stream);
