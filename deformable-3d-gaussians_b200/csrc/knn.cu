@@ -120,10 +120,48 @@ __global__ void __launch_bounds__(256) knn_bbox_kernel(int P, const float* __res
   }
 }
 
-__global__ void knn_plan_kernel(int P, int cell_cap, const uint32_t* bbox, KnnPlan* plan) {
+// Robust extent of the cloud.  A few far outliers (COLMAP clouds have them) would stretch a grid laid over the raw
+// bounding box until the whole dense part falls into a handful of cells and the query degenerates to all-pairs.  Three
+// passes of "mean +- 4 sigma of the points inside the current box" shrink the box onto the bulk; points outside are
+// clamped into its boundary cells by knn_cell, which keeps the search exact (a clamped point is at least as far away
+// as the cell it is filed under, so the shell bound stays a lower bound).  mom: [count, sum xyz, sum of squares xyz].
+__global__ void __launch_bounds__(256)
+knn_moments_kernel(int P, const float* __restrict__ pts, const float* __restrict__ box, double* mom) {
+  double acc[7] = {0, 0, 0, 0, 0, 0, 0};
+  const float lo[3] = {box[0], box[1], box[2]}, hi[3] = {box[3], box[4], box[5]};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < P; i += gridDim.x * blockDim.x) {
+    const float x = pts[3 * (size_t)i], y = pts[3 * (size_t)i + 1], z = pts[3 * (size_t)i + 2];
+    if (x >= lo[0] && x <= hi[0] && y >= lo[1] && y <= hi[1] && z >= lo[2] && z <= hi[2]) {
+      acc[0] += 1.0; acc[1] += x; acc[2] += y; acc[3] += z;
+      acc[4] += (double)x * x; acc[5] += (double)y * y; acc[6] += (double)z * z;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 7; k++) {
+    for (int o = 16; o; o >>= 1) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], o);
+    if ((threadIdx.x & 31) == 0 && acc[k] != 0.0) atomicAdd(&mom[k], acc[k]);
+  }
+}
+// box <- (mean +- 4 sigma) intersected with box; pass 0 starts from the raw bounding box
+__global__ void knn_trim_kernel(const uint32_t* bbox, int first, double* mom, float* box) {
+  if (first) {
+    for (int c = 0; c < 6; c++) box[c] = knn_dec(bbox[c]);
+  } else if (mom[0] >= 8.0) {
+    for (int c = 0; c < 3; c++) {
+      const double mean = mom[1 + c] / mom[0];
+      const double var = fmax(mom[4 + c] / mom[0] - mean * mean, 0.0);
+      const double sd = sqrt(var);
+      const float lo = (float)(mean - 4.0 * sd), hi = (float)(mean + 4.0 * sd);
+      if (lo < hi) { box[c] = fmaxf(box[c], lo); box[3 + c] = fminf(box[3 + c], hi); }
+    }
+  }
+  for (int k = 0; k < 7; k++) mom[k] = 0.0;
+}
+
+__global__ void knn_plan_kernel(int P, int cell_cap, const float* box, KnnPlan* plan) {
   KnnPlan pl;
-  pl.minx = knn_dec(bbox[0]); pl.miny = knn_dec(bbox[1]); pl.minz = knn_dec(bbox[2]);
-  const float ex = knn_dec(bbox[3]) - pl.minx, ey = knn_dec(bbox[4]) - pl.miny, ez = knn_dec(bbox[5]) - pl.minz;
+  pl.minx = box[0]; pl.miny = box[1]; pl.minz = box[2];
+  const float ex = box[3] - pl.minx, ey = box[4] - pl.miny, ez = box[5] - pl.minz;
   const float me = fmaxf(ex, fmaxf(ey, ez));
   if (!(me > 0.f) || !(me < FLT_MAX)) {          // all points coincide (or non-finite input): one cell
     pl.h = 1.f; pl.inv_h = 0.f; pl.gx = pl.gy = pl.gz = 1;
@@ -169,14 +207,23 @@ knn_scatter_kernel(int P, const float* __restrict__ pts, const uint32_t* __restr
       make_float4(pts[3 * (size_t)i], pts[3 * (size_t)i + 1], pts[3 * (size_t)i + 2], __int_as_float(i));
 }
 
+constexpr int kKnnOutlierCap = 4096;
+
 __global__ void __launch_bounds__(128)
 knn_grid_query_kernel(int P, const KnnPlan* __restrict__ plan, const uint32_t* __restrict__ starts,
-                      const float4* __restrict__ sorted, float* __restrict__ out) {
+                      const float4* __restrict__ sorted, float* __restrict__ out, const float* __restrict__ box,
+                      uint32_t* __restrict__ outliers) {
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= P) return;
   const KnnPlan pl = *plan;
   const float4 me = sorted[s];
   const int self = __float_as_int(me.w);
+  // a point outside the trimmed box has its neighbours far away in grid units: its shell walk would visit the whole
+  // grid in one thread.  It goes on a (short) list instead and gets a CTA of its own (knn_outlier_kernel).
+  if (me.x < box[0] || me.y < box[1] || me.z < box[2] || me.x > box[3] || me.y > box[4] || me.z > box[5]) {
+    const uint32_t slot = atomicAdd(&outliers[0], 1u);
+    if (slot < (uint32_t)kKnnOutlierCap) { outliers[1 + slot] = (uint32_t)s; return; }
+  }
   const int3 c = knn_cell(pl, me.x, me.y, me.z);
   float b0 = FLT_MAX, b1 = FLT_MAX, b2 = FLT_MAX;
   auto scan = [&](uint32_t a, uint32_t b) {
@@ -185,6 +232,7 @@ knn_grid_query_kernel(int P, const KnnPlan* __restrict__ plan, const uint32_t* _
       const float3 d = {p.x - me.x, p.y - me.y, p.z - me.z};
       const float dist = ff(d.z, d.z, ff(d.x, d.x, fm(d.y, d.y)));
       if (b2 > dist && __float_as_int(p.w) != self) knn_insert(dist, b0, b1, b2);
+      if (b2 == 0.0f) return;   // three coincident neighbours: nothing can improve (clouds with many duplicates)
     }
   };
   const int rmax = max(pl.gx, max(pl.gy, pl.gz));
@@ -207,9 +255,35 @@ knn_grid_query_kernel(int P, const KnnPlan* __restrict__ plan, const uint32_t* _
     // every unvisited point sits in a cell at Chebyshev offset >= r+1, i.e. at distance >= r*h (minus the cell
     // assignment's rounding, <= 2e-4 h): stop once the third-best distance is safely below that
     const float reach = (float)r * pl.h;
-    if (b2 < reach * reach * 0.999f) break;
+    if (b2 < reach * reach * 0.999f || b2 == 0.0f) break;
   }
   out[self] = (b0 + b1 + b2) / 3.0f;
+}
+
+// one CTA per listed outlier: all P points scanned by 256 threads, the per-thread three best merged by thread 0
+__global__ void __launch_bounds__(256)
+knn_outlier_kernel(int P, const float4* __restrict__ sorted, const uint32_t* __restrict__ outliers,
+                   float* __restrict__ out) {
+  const uint32_t n = min(outliers[0], (uint32_t)kKnnOutlierCap);
+  if (blockIdx.x >= n) return;
+  const float4 me = sorted[outliers[1 + blockIdx.x]];
+  const int self = __float_as_int(me.w);
+  float b0 = FLT_MAX, b1 = FLT_MAX, b2 = FLT_MAX;
+  for (int k = threadIdx.x; k < P; k += blockDim.x) {
+    const float4 p = sorted[k];
+    const float3 d = {p.x - me.x, p.y - me.y, p.z - me.z};
+    const float dist = ff(d.z, d.z, ff(d.x, d.x, fm(d.y, d.y)));
+    if (b2 > dist && __float_as_int(p.w) != self) knn_insert(dist, b0, b1, b2);
+  }
+  __shared__ float cand[3 * 256];
+  cand[3 * threadIdx.x] = b0; cand[3 * threadIdx.x + 1] = b1; cand[3 * threadIdx.x + 2] = b2;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float c0 = FLT_MAX, c1 = FLT_MAX, c2 = FLT_MAX;
+    for (int k = 0; k < 3 * 256; k++)
+      if (c2 > cand[k]) knn_insert(cand[k], c0, c1, c2);
+    out[self] = (c0 + c1 + c2) / 3.0f;
+  }
 }
 
 }  // namespace d3g
@@ -227,13 +301,16 @@ extern "C" int d3g_knn_mean_dist2(int32_t P, const float* points, float* mean_di
 
 // workspace layout of the grid path (all offsets 256-byte aligned)
 namespace {
-struct KnnLayout { size_t bbox, plan, counts, starts, cell_of, rank_of, sorted, cub, cub_bytes, total; int cell_cap; };
+struct KnnLayout { size_t bbox, box, mom, outliers, plan, counts, starts, cell_of, rank_of, sorted, cub, cub_bytes, total; int cell_cap; };
 KnnLayout knn_layout(int32_t P) {
   KnnLayout L;
   L.cell_cap = P / 2 + 4096;
   size_t o = 0;
   auto take = [&](size_t bytes) { const size_t at = o; o = d3g::align_up(o + bytes, 256); return at; };
   L.bbox = take(6 * sizeof(uint32_t));
+  L.box = take(6 * sizeof(float));
+  L.mom = take(7 * sizeof(double));
+  L.outliers = take((size_t)(1 + d3g::kKnnOutlierCap) * sizeof(uint32_t));
   L.plan = take(sizeof(KnnPlan));
   L.counts = take((size_t)(L.cell_cap + 1) * sizeof(uint32_t));
   L.starts = take((size_t)(L.cell_cap + 1) * sizeof(uint32_t));
@@ -274,13 +351,23 @@ extern "C" int d3g_knn_mean_dist2_grid(int32_t P, const float* points, float* me
   cudaMemsetAsync(counts, 0, (size_t)(L.cell_cap + 1) * sizeof(uint32_t), stream);
   const int nb = (P + 255) / 256;
   knn_bbox_kernel<<<min(nb, 148 * 4), 256, 0, stream>>>(P, points, bbox);
-  knn_plan_kernel<<<1, 1, 0, stream>>>(P, L.cell_cap, bbox, plan);
+  float* box = (float*)(ws + L.box);
+  double* mom = (double*)(ws + L.mom);
+  knn_trim_kernel<<<1, 1, 0, stream>>>(bbox, 1, mom, box);
+  for (int pass = 0; pass < 3; pass++) {
+    knn_moments_kernel<<<min(nb, 148 * 4), 256, 0, stream>>>(P, points, box, mom);
+    knn_trim_kernel<<<1, 1, 0, stream>>>(bbox, 0, mom, box);
+  }
+  knn_plan_kernel<<<1, 1, 0, stream>>>(P, L.cell_cap, box, plan);
   knn_count_kernel<<<nb, 256, 0, stream>>>(P, points, plan, counts, cell_of, rank_of);
   size_t cub_bytes = L.cub_bytes;
   cudaError_t e = cub::DeviceScan::ExclusiveSum(ws + L.cub, cub_bytes, counts, starts, L.cell_cap + 1, stream);
   if (e != cudaSuccess) return set_err(D3G_ERR_CUDA, "knn scan failed: %s", cudaGetErrorString(e));
   knn_scatter_kernel<<<nb, 256, 0, stream>>>(P, points, starts, cell_of, rank_of, sorted);
-  knn_grid_query_kernel<<<(P + 127) / 128, 128, 0, stream>>>(P, plan, starts, sorted, mean_dist2);
+  uint32_t* outliers = (uint32_t*)(ws + L.outliers);
+  cudaMemsetAsync(outliers, 0, sizeof(uint32_t), stream);
+  knn_grid_query_kernel<<<(P + 127) / 128, 128, 0, stream>>>(P, plan, starts, sorted, mean_dist2, box, outliers);
+  knn_outlier_kernel<<<kKnnOutlierCap, 256, 0, stream>>>(P, sorted, outliers, mean_dist2);
   D3G_LAUNCH_CHECK(0, stream);
   return 0;
 }

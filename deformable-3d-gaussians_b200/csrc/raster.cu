@@ -864,8 +864,11 @@ __device__ __forceinline__ float bfly(float lo, float hi, bool up, int mask) {
 
 static constexpr int kAccStride = 12;  // floats per Gaussian in the shared accumulator
 
+// kDepth: a depth cotangent exists (the reference never back-propagates through depth, so the usual instantiation
+// drops the fourth channel's recurrence and its gradient term); kDensify: semantics of the densify buffer.
+template <bool kDepth, int kDensify>
 __global__ void __launch_bounds__(kBlock)
-render_bwd_kernel(int H, int W, int gx, int densify_mode, const float* __restrict__ bg,
+render_bwd_kernel(int H, int W, int gx, const float* __restrict__ bg,
                   const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                   const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
                   const float4* __restrict__ rgbd, const float* __restrict__ final_T,
@@ -895,7 +898,7 @@ render_bwd_kernel(int H, int W, int gx, int densify_mode, const float* __restric
   float dLp0 = 0.f, dLp1 = 0.f, dLp2 = 0.f, dLd = 0.f;
   if (inside) {
     dLp0 = dL_dpix[pix]; dLp1 = dL_dpix[P + pix]; dLp2 = dL_dpix[2 * P + pix];
-    if (dL_ddepth) dLd = dL_ddepth[pix];
+    if (kDepth) dLd = dL_ddepth[pix];
   }
   const float bgT = -T_final * (__ldg(bg) * dLp0 + __ldg(bg + 1) * dLp1 + __ldg(bg + 2) * dLp2);
   float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, ard = 0.f;
@@ -971,8 +974,11 @@ render_bwd_kernel(int H, int W, int gx, int densify_mode, const float* __restric
         ar0 = last_alpha * lc0 + (1.0f - last_alpha) * ar0; lc0 = cd.x;
         ar1 = last_alpha * lc1 + (1.0f - last_alpha) * ar1; lc1 = cd.y;
         ar2 = last_alpha * lc2 + (1.0f - last_alpha) * ar2; lc2 = cd.z;
-        ard = last_alpha * ld + (1.0f - last_alpha) * ard;  ld = cd.w;
-        float dL_dalpha = (cd.x - ar0) * dLp0 + (cd.y - ar1) * dLp1 + (cd.z - ar2) * dLp2 + (cd.w - ard) * dLd;
+        float dL_dalpha = (cd.x - ar0) * dLp0 + (cd.y - ar1) * dLp1 + (cd.z - ar2) * dLp2;
+        if (kDepth) {
+          ard = last_alpha * ld + (1.0f - last_alpha) * ard;  ld = cd.w;
+          dL_dalpha += (cd.w - ard) * dLd;
+        }
         dL_dalpha = dL_dalpha * T + bgT * inv;
         last_alpha = alpha;
         const float dL_dG = co.w * dL_dalpha;
@@ -984,15 +990,15 @@ render_bwd_kernel(int H, int W, int gx, int densify_mode, const float* __restric
         const float g_mx = dL_dG * dG_ddelx * ddelx_dx;
         const float g_my = dL_dG * dG_ddely * ddely_dy;
         v[0] = g_mx; v[1] = g_my;
-        if (densify_mode == 1) { v[2] = g_mx; v[3] = g_my; }
-        else if (densify_mode == 2) { v[2] = fabsf(g_mx); v[3] = fabsf(g_my); }
+        if (kDensify == 1) { v[2] = g_mx; v[3] = g_my; }
+        else if (kDensify == 2) { v[2] = fabsf(g_mx); v[3] = fabsf(g_my); }
         else { v[2] = sqrtf(g_mx * g_mx + g_my * g_my); }
         const float hG = -0.5f * dL_dG;
         v[4] = hG * gdx * dx;
         v[5] = hG * gdx * dy;
         v[6] = hG * gdy * dy;
         v[7] = G * dL_dalpha;
-        v[8] = dch * dLp0; v[9] = dch * dLp1; v[10] = dch * dLp2; v[11] = dch * dLd;
+        v[8] = dch * dLp0; v[9] = dch * dLp1; v[10] = dch * dLp2; v[11] = kDepth ? dch * dLd : 0.f;
       }
       // split butterfly: 12 -> 6 -> 3 -> 2 -> 1 values per lane, 13 shuffles
       float a6[6], b3[3];
@@ -1461,9 +1467,15 @@ int d3g_raster_backward(const d3g_raster_settings* s, int32_t N, uint64_t cap, c
   if ((size_t)a.gx * a.gy > 0) {
     dim3 grid(a.gx, a.gy);
     { ProfScope _p(PROF_RENDER_BWD, stream);
-    render_bwd_kernel<<<grid, kBlock, 0, stream>>>(a.H, a.W, a.gx, a.densify_mode, a.bg, im.ranges, b.point_list,
-                                                   g.means2D, g.conic_opacity, g.rgbd, im.final_T, im.n_contrib,
-                                                   dL_dcolor, dL_ddepth, g.acc_mean, g.acc_conic, g.acc_color);
+#define D3G_RBWD(DEPTH, MODE)                                                                                   \
+    render_bwd_kernel<DEPTH, MODE><<<grid, kBlock, 0, stream>>>(a.H, a.W, a.gx, a.bg, im.ranges, b.point_list,       \
+                                                                g.means2D, g.conic_opacity, g.rgbd, im.final_T,     \
+                                                                im.n_contrib, dL_dcolor, dL_ddepth, g.acc_mean,     \
+                                                                g.acc_conic, g.acc_color)
+    const int dm = a.densify_mode == 1 ? 1 : (a.densify_mode == 2 ? 2 : 3);
+    if (dL_ddepth) { if (dm == 1) D3G_RBWD(true, 1); else if (dm == 2) D3G_RBWD(true, 2); else D3G_RBWD(true, 3); }
+    else { if (dm == 1) D3G_RBWD(false, 1); else if (dm == 2) D3G_RBWD(false, 2); else D3G_RBWD(false, 3); }
+#undef D3G_RBWD
     D3G_LAUNCH_CHECK(s->debug, stream); }
   }
   { ProfScope _p(PROF_PREPROCESS_BWD, stream);

@@ -84,6 +84,36 @@ def test_full_size_against_reference_and_properties():
     open("gpurun_out/knn_timing.txt", "w").write(msg + "\n")
 
 
+@pytest.mark.parametrize("kind", ["outliers", "duplicates"])
+def test_large_cloud_with_outliers_or_duplicates_stays_fast_and_exact(kind):
+    """300k points whose bounding box is a poor guide to their density: a unit cube plus twenty points thousands of
+    units away (the grid is laid over a trimmed box, outliers are clamped into its boundary cells), or a cloud with a
+    100k-fold duplicated point (the scan of a cell stops at three coincident neighbours).  Exact against the compiled
+    reference, and nowhere near the seconds an all-pairs scan of a few cells would take."""
+    g = torch.Generator().manual_seed(5)
+    P = 300000
+    pts = torch.rand(P, 3, generator=g) * 2.0 - 1.0
+    if kind == "outliers":
+        pts[:20] = (torch.rand(20, 3, generator=g) - 0.5) * 2e4
+    else:
+        pts[:100000] = torch.tensor([0.25, -0.5, 0.125])
+    pts = pts.cuda()
+    knn.distCUDA2(pts)
+    torch.cuda.synchronize()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev[0].record(); got = knn.distCUDA2(pts); ev[1].record(); torch.cuda.synchronize()
+    ms = ev[0].elapsed_time(ev[1])
+    assert ms < 50.0, "distCUDA2 took %.1f ms on the %s cloud" % (ms, kind)
+    if os.path.exists(knn_oracle.REF_SO):
+        assert torch.equal(got, knn_oracle.reference_mean_dist2(pts))
+    else:
+        sel = torch.randperm(P, generator=g)[:2000].cuda()
+        d = torch.cdist(pts[sel].double(), pts.double()) ** 2
+        d[torch.arange(2000), sel] = float("inf")
+        want = d.topk(3, largest=False).values.mean(1)
+        assert torch.allclose(got[sel].double(), want, rtol=1e-5, atol=1e-12)
+
+
 def test_argument_errors():
     with pytest.raises(RuntimeError):
         knn.distCUDA2(torch.zeros(4, 3))
