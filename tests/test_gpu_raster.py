@@ -142,7 +142,8 @@ def _rel(a, b):
 
 @pytest.mark.parametrize("N,H,W,scale_mul,mode,with_depth", [
     (3000, 128, 128, 2.0, 2, False), (3000, 128, 128, 2.0, 1, True), (6000, 200, 312, 1.5, 3, False),
-    (50000, 400, 400, 1.0, 2, False)])
+    (50000, 400, 400, 1.0, 2, False),
+    (100000, 800, 800, 1.0, 2, False)])      # config C2 at full size
 def test_backward_matches_oracle(N, H, W, scale_mul, mode, with_depth):
     rast = pkg("rasterizer")
     g, cam, bg = _scene(N, H, W, seed=N + 1, scale_mul=scale_mul)

@@ -244,3 +244,60 @@ def test_fused_densification_stats_match_reference_ops():
     frames.add_densification_stats(g, out)
     assert torch.equal(g.max_radii2D, mr_r) and torch.equal(g.denom, den_r)
     assert torch.allclose(g.xyz_gradient_accum, acc_r, rtol=1e-6, atol=0)
+
+
+def test_graphed_step_matches_eager_and_sees_optimizer_updates():
+    """frames.GraphedStep: the whole deform -> render -> loss -> backward step replayed as one CUDA graph gives the
+    eager step's loss and gradients, and — because the weight re-pack is part of the graph — keeps doing so after the
+    fused Adam has moved the parameters between replays."""
+    frames, synth, renderer, deform = pkg("frames"), pkg("synth"), pkg("renderer"), pkg("deform")
+    rast, loss_utils, optim = pkg("rasterizer"), pkg("loss_utils"), pkg("optim")
+    dev = torch.device("cuda", 0)
+    N, H, W = 5000, 96, 128
+    g = synth.SynthGaussians(N, seed=11, sh_degree=3)
+    for name in ("_xyz", "_features_dc", "_features_rest", "_opacity", "_scaling", "_rotation"):
+        setattr(g, name, getattr(g, name).to(dev).requires_grad_(True))
+    cam = synth.camera_to(synth.make_camera(W, H, theta_deg=25.0, fid=0.4), dev)
+    pipe = type("Pipe", (), dict(convert_SHs_python=False, compute_cov3D_python=False, debug=False))()
+    torch.manual_seed(3)
+    model = deform.DeformModelBaseline(is_blender=True)
+    with torch.no_grad():
+        for m in (model.deform.gaussian_warp, model.deform.gaussian_rotation, model.deform.gaussian_scaling):
+            m.weight.mul_(0.05); m.bias.mul_(0.05)
+    params = g.parameters() + list(model.deform.parameters())
+    flat = frames.FlatGrads(params)
+    opt = optim.Adam([{"params": list(model.deform.parameters()), "lr": 1e-3}], lr=0.0, eps=1e-15)
+    gt = torch.rand(3, H, W, device=dev)
+    bg = torch.zeros(3, device=dev)
+    loss_out = torch.zeros(1, device=dev)
+    old_policy = rast.PAIR_CAPACITY_POLICY
+    policy = rast.GrowingPairCapacity(1.5)
+    rast.PAIR_CAPACITY_POLICY = policy
+
+    def step():
+        flat.zero()
+        t = cam.fid.unsqueeze(0).expand(N, -1)
+        d_xyz, d_rot, d_scale = model.step(g.get_xyz.detach(), t)
+        out = renderer.render(cam, g, pipe, bg, d_xyz, d_rot, d_scale)
+        loss = loss_utils.training_loss(out["render"], gt, 0.2)
+        loss.backward()
+        loss_out.copy_(loss.detach().reshape(1))
+        return loss_out
+
+    try:
+        step(); step()                                   # eager: the capacity policy sees the shape
+        graphed = frames.GraphedStep(step, warmup=2, checks=[policy.check, model.deform.check_status])
+        for it in range(3):
+            step()
+            torch.cuda.synchronize()
+            want_loss, want_grad = float(loss_out), flat.flat.clone()
+            graphed()
+            torch.cuda.synchronize()
+            assert abs(float(loss_out) - want_loss) <= 1e-6 * abs(want_loss), it
+            err = float((flat.flat - want_grad).abs().max() / want_grad.abs().max())
+            assert err < 1e-5, (it, err)                  # (split-K sums land through atomics: fp32 order noise only)
+            graphed.check()
+            opt.step()                                    # parameters move; the next replay must use the new weights
+        assert not torch.equal(flat.flat, torch.zeros_like(flat.flat))
+    finally:
+        rast.PAIR_CAPACITY_POLICY = old_policy
