@@ -194,7 +194,9 @@ class Workload:
                                           early=len(g.parameters()) if self.early else 0)
             if self.early:
                 pkg("_lib").load().d3g_mlp_sm_reserve(int(os.environ.get("D3G_BENCH_SM_RESERVE", "8")))
-            self.grads.frames_per_reduce = max(len(self.mine), 1)
+            # one backward() covers all of this rank's frames (their losses are summed first), so every parameter's
+            # gradient is accumulated once per step: the early slice is complete after ONE accumulation per parameter
+            self.grads.frames_per_reduce = 1
             self.flat = self.grads.flat
             # MLP backward adds straight into those .grad views (no per-parameter zero-fill + AccumulateGrad add)
             self.model.deform.fused_grad_accumulation = True
@@ -643,6 +645,16 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=device)
+        # a rank that blocks in a collective (a peer died, mismatched collectives) must not hold N GPUs until some outer
+        # limit fires: the whole default run takes well under a minute
+        wd = float(os.environ.get("D3G_BENCH_WATCHDOG_S", "240"))
+
+        def _watchdog():
+            print("bench.py: rank %d made no exit within %.0f s — aborting" % (rank, wd), file=sys.stderr, flush=True)
+            os._exit(3)
+        t = threading.Timer(wd, _watchdog)
+        t.daemon = True
+        t.start()
     work = Workload(cfg, rank, world, device)
 
     warm = max(args.warmup, 3)

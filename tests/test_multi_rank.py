@@ -63,6 +63,45 @@ def test_two_rank_gradient_sum_matches_serial(tmp_path):
     assert got["stats"][0].item() == 3.0 and got["stats"][1].item() == 4.0 and got["stats"][2].item() == 5.0
 
 
+def _worker_summed(rank, world, port, T, out):
+    """bench.py's shape: the losses of a rank's frames are summed and back-propagated ONCE per step (one gradient
+    accumulation per parameter, whatever the rank's frame count), several steps in a row, uneven shards."""
+    import importlib
+    import sys
+    sys.path.insert(0, ROOT)
+    frames = importlib.import_module(PKG + ".frames")
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.manual_seed(0)
+    params = [torch.randn(3, 2, requires_grad=True), torch.randn(2, requires_grad=True)]
+    fg = frames.FlatGrads(params, early=1)
+    fg.frames_per_reduce = 1
+    mine = frames.shard_frames(T, world, rank)
+    results = []
+    for step in range(3):
+        fg.zero()
+        if mine:
+            sum(_frame_loss(params, k) for k in mine).backward()
+        fg.all_reduce()
+        results.append(fg.flat.clone())
+    if rank == 0:
+        torch.save(results, out)
+    dist.destroy_process_group()
+
+
+def test_uneven_shards_with_one_backward_per_step(tmp_path):
+    T, world = 3, 2          # shards of 2 and 1 frames
+    out = str(tmp_path / "r0.pt")
+    mp.spawn(_worker_summed, args=(world, _free_port(), T, out), nprocs=world, join=True)
+    got = torch.load(out)
+    torch.manual_seed(0)
+    params = [torch.randn(3, 2, requires_grad=True), torch.randn(2, requires_grad=True)]
+    sum(_frame_loss(params, k) for k in range(T)).backward()
+    for flat in got:      # every step reduces the same sums: no step may be skipped or doubled
+        assert torch.allclose(flat[:6].view(3, 2), params[0].grad, rtol=1e-6, atol=1e-6)
+        assert torch.allclose(flat[8:10], params[1].grad, rtol=1e-6, atol=1e-6)
+
+
 def test_shard_and_weights():
     import importlib
     frames = importlib.import_module(PKG + ".frames")
