@@ -411,7 +411,8 @@ def roofline(table, R, cfg, pk, rows_per_mlp_launch, traffic=None):
     # bytes each rasterizer stage must move once (inputs read once, outputs written once)
     algo_bytes = {
         "preprocess_fwd": 311 * N, "scan": 8 * N, "duplicate_with_keys": 20 * N + 12 * R, "radix_sort": 24 * R,
-        "tile_sort": 24 * R, "identify_tile_ranges": 8 * R + 8 * Tl, "render_fwd": 44 * R + 24 * P,
+        "tile_sort": 24 * R, "tile_count": 12 * N + 4 * R, "tile_scatter": 28 * N + 12 * R, "tile_scan": 16 * Tl,
+        "identify_tile_ranges": 8 * R + 8 * Tl, "render_fwd": 44 * R + 24 * P,
         "render_bwd": 88 * R + 32 * P, "preprocess_bwd": 600 * N,
     }
     # ALGORITHMIC flops per point (519,936 MAC forward incl. heads; dgrad chain 7*65536+16*256 MAC, wgrad = forward

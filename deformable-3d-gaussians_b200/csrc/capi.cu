@@ -38,7 +38,7 @@ void prof_end(int id, cudaStream_t stream) {
 
 static const char* kProfNames[d3g::PROF_COUNT] = {
     "preprocess_fwd", "scan", "duplicate_with_keys", "pad_keys", "radix_sort", "identify_tile_ranges", "render_fwd",
-    "render_bwd", "preprocess_bwd", "mlp_tfeat", "mlp_fwd", "mlp_dgrad", "mlp_wgrad", "mlp_finish", "mlp_pack_weights", "image_loss_fwd", "image_loss_bwd", "adam_step", "mlp_input_bwd", "densification_stats", "tile_sort"};
+    "render_bwd", "preprocess_bwd", "mlp_tfeat", "mlp_fwd", "mlp_dgrad", "mlp_wgrad", "mlp_finish", "mlp_pack_weights", "image_loss_fwd", "image_loss_bwd", "adam_step", "mlp_input_bwd", "densification_stats", "tile_sort", "tile_count", "tile_scan", "tile_scatter", "mlp_amax"};
 
 extern "C" {
 int d3g_prof_enable(int32_t on) { d3g::g_prof_on = on != 0; return 0; }

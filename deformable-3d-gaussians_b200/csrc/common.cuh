@@ -35,7 +35,7 @@ int set_err(int code, const char* fmt, ...);
 enum ProfId {
   PROF_PREPROCESS_FWD = 0, PROF_SCAN, PROF_DUPLICATE, PROF_PAD_KEYS, PROF_SORT, PROF_RANGES, PROF_RENDER_FWD,
   PROF_RENDER_BWD, PROF_PREPROCESS_BWD, PROF_MLP_TFEAT, PROF_MLP_FWD, PROF_MLP_DGRAD, PROF_MLP_WGRAD,
-  PROF_MLP_FINISH, PROF_MLP_PACK, PROF_LOSS_FWD, PROF_LOSS_BWD, PROF_ADAM, PROF_MLP_DPE, PROF_DENSIFY, PROF_TILE_SORT, PROF_COUNT
+  PROF_MLP_FINISH, PROF_MLP_PACK, PROF_LOSS_FWD, PROF_LOSS_BWD, PROF_ADAM, PROF_MLP_DPE, PROF_DENSIFY, PROF_TILE_SORT, PROF_TILE_COUNT, PROF_TILE_SCAN, PROF_TILE_SCATTER, PROF_MLP_AMAX, PROF_COUNT
 };
 extern bool g_prof_on;
 void prof_begin(int id, cudaStream_t stream);

@@ -1042,7 +1042,7 @@ static int mlp_backward_impl(const d3g_mlp_config* cfg, const void* packed, cons
     a.g_scale = (cfg->heads & 4) ? dL_dscale : nullptr;
     a.dz_img = ws.dz_img; a.dout_img = ws.dout_img; a.headb_acc = headb_acc; a.abort_flag = ws.status;
     a.amax_bits = amax_bits; a.gain_e = gain_e; a.gtarget = gtarget;
-    { ProfScope _p(PROF_MLP_FINISH, stream);
+    { ProfScope _p(PROF_MLP_AMAX, stream);
       mlp_amax_kernel<<<2 * num_sms(), 256, 0, stream>>>(a);
       D3G_LAUNCH_CHECK(0, stream); }
     size_t smem = BwdSmem::total + 1024;

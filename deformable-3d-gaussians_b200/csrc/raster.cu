@@ -1396,14 +1396,14 @@ int d3g_raster_render(const d3g_raster_settings* s, int32_t N, uint64_t cap, voi
   if (a.binning_mode == 0 && N > 0) {
     if (tiles > 0x7fffffffu) return set_err(D3G_ERR_CAPACITY, "too many tiles");
     D3G_CUDA_TRY(cudaMemsetAsync(im.tile_count, 0, tiles * kTileCtrStride * sizeof(uint32_t), stream));
-    { ProfScope _p(PROF_DUPLICATE, stream);
+    { ProfScope _p(PROF_TILE_COUNT, stream);
       tile_count_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, a.gx, a.gy, g.means2D, radii, im.tile_count);
       D3G_LAUNCH_CHECK(s->debug, stream); }
-    { ProfScope _p(PROF_SCAN, stream);
+    { ProfScope _p(PROF_TILE_SCAN, stream);
       tile_scan_kernel<<<1, 1024, 0, stream>>>((int)tiles, cap, im.tile_count, im.tile_cursor, im.ranges, g.header);
       D3G_LAUNCH_CHECK(s->debug, stream); }
     if (cap > 0) {
-      { ProfScope _p(PROF_DUPLICATE, stream);
+      { ProfScope _p(PROF_TILE_SCATTER, stream);
         tile_scatter_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, a.gx, a.gy, g.means2D, g.rgbd, radii, im.tile_cursor,
                                                                b.keys_unsorted, g.header);
         D3G_LAUNCH_CHECK(s->debug, stream); }

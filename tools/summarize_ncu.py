@@ -67,7 +67,8 @@ def traffic(path, out, title):
     names = {"render_fwd_kernel": "render_fwd", "render_bwd_kernel": "render_bwd", "mlp_fwd_kernel": "mlp_fwd",
              "mlp_dgrad_kernel": "mlp_dgrad", "mlp_wgrad_kernel": "mlp_wgrad", "preprocess_fwd_kernel": "preprocess_fwd",
              "preprocess_bwd_kernel": "preprocess_bwd", "duplicate_with_keys_kernel": "duplicate_with_keys",
-             "DeviceRadixSortOnesweepKernel": "radix_sort_pass"}
+             "DeviceRadixSortOnesweepKernel": "radix_sort_pass", "tile_sort_kernel": "tile_sort",
+             "tile_count_kernel": "tile_count", "tile_scatter_kernel": "tile_scatter"}
     acc = {}
     for r in rows[2:]:
         for pat, short in names.items():
