@@ -287,4 +287,62 @@ int d3g_image_loss_backward(int32_t C, int32_t H, int32_t W, const float* img, c
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------------
+// d3g_image_loss_static: the same loss + gradient for callers that may not allocate (no counterpart in the reference).
+// The workspace d3g_image_loss takes from its caller (three per-pixel
+// partial maps + the per-block partial sums) lives in a file-scope device array instead, so the call performs no
+// cudaMalloc / cudaFree and asks nothing of the caller's allocator.  Every GPU that loads libd3g.so holds the array
+// (24.1 MiB) until the process exits.
+//
+// In host code `g_loss_scratch` is only a host-side stand-in for the symbol, never a device address: the device
+// address is looked up once per device, with that device current, through cudaGetSymbolAddress.
+// ------------------------------------------------------------------------------------------------
+}  // extern "C"
+
+namespace d3g {
+constexpr size_t kStaticLossMaxElems = (size_t)1 << 21;    // C*H*W of one call (3 x 800 x 800 = 1,920,000 fits)
+constexpr size_t kStaticLossMaxBlocks = (size_t)1 << 14;   // C * ceil(H/16) * ceil(W/32) of one call
+constexpr size_t kStaticLossBytes = 3 * kStaticLossMaxElems * sizeof(float)        // dS/dmu1, dS/dE[x^2], dS/dE[xy]
+                                    + 2 * kStaticLossMaxBlocks * sizeof(float);   // per-block {sum S, sum |x-y|}
+static __device__ __align__(256) unsigned char g_loss_scratch[kStaticLossBytes];
+static void* g_loss_scratch_ptr[64] = {};   // per device: the symbol's address on that device
+}  // namespace d3g
+
+extern "C" {
+
+int d3g_image_loss_static_limits(size_t* max_elements, size_t* max_blocks, size_t* scratch_bytes) {
+  if (max_elements) *max_elements = kStaticLossMaxElems;
+  if (max_blocks) *max_blocks = kStaticLossMaxBlocks;
+  if (scratch_bytes) *scratch_bytes = kStaticLossBytes;
+  return 0;
+}
+
+int d3g_image_loss_static(int32_t C, int32_t H, int32_t W, const float* img, const float* gt, float w_l1,
+                          float w_ssim, float bias, float* out3, float* dL_dimg, void* stream_) {
+  if (C < 1 || H < 1 || W < 1) return set_err(D3G_ERR_INVALID, "bad image_loss shape");
+  if (!img || !gt || !out3) return set_err(D3G_ERR_INVALID, "NULL argument");
+  const size_t n = (size_t)C * H * W;
+  const size_t blocks = (size_t)C * ((H + kTH - 1) / kTH) * ((W + kTW - 1) / kTW);
+  if (n > kStaticLossMaxElems)
+    return set_err(D3G_ERR_CAPACITY, "d3g_image_loss_static: C*H*W = %zu exceeds the static scratch limit of %zu elements "
+                   "(use d3g_image_loss with a caller-provided workspace)", n, (size_t)kStaticLossMaxElems);
+  if (blocks > kStaticLossMaxBlocks)
+    return set_err(D3G_ERR_CAPACITY, "d3g_image_loss_static: %zu 32x16 pixel blocks exceed the static scratch limit of %zu "
+                   "(use d3g_image_loss with a caller-provided workspace)", blocks, (size_t)kStaticLossMaxBlocks);
+  int dev = 0;
+  D3G_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return set_err(D3G_ERR_UNSUPPORTED, "d3g_image_loss_static: device index %d above 63", dev);
+  if (!g_loss_scratch_ptr[dev]) {   // set-up, once per device, with that device current
+    void* ptr = nullptr;
+    D3G_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_loss_scratch));
+    if (!ptr) return set_err(D3G_ERR_CUDA, "d3g_image_loss_static: cudaGetSymbolAddress returned NULL");
+    g_loss_scratch_ptr[dev] = ptr;
+  }
+  // Same kernels, same workspace layout as d3g_image_loss (which sizes the layout from this call's n and blocks, both
+  // within the array by the checks above).  Nothing in the array has to start at zero: every word a kernel reads
+  // (the partial maps at in-image pixels, the block sums) is written earlier in the same call, so the contents the
+  // previous call left behind are never seen.
+  return d3g_image_loss(C, H, W, img, gt, w_l1, w_ssim, bias, g_loss_scratch_ptr[dev], out3, dL_dimg, stream_);
+}
+
 }  // extern "C"

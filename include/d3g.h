@@ -150,6 +150,20 @@ int d3g_image_loss(int32_t C, int32_t H, int32_t W, const float* img, const floa
 int d3g_image_loss_backward(int32_t C, int32_t H, int32_t W, const float* img, const float* gt, float w_l1,
                             float w_ssim, const void* workspace, const float* upstream, float* dL_dimg,
                             void* stream);
+/* d3g_image_loss for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.  Same inputs,
+ * outputs and results as d3g_image_loss, but the workspace is a static device array inside the library (24.1 MiB, held
+ * by every GPU that loads the library until the process exits), so the call performs no cudaMalloc / cudaFree and needs
+ * no allocator from its caller.  Limits: C*H*W <= 2^21 elements (3 x 800 x 800 fits) and
+ * C * ceil(H/16) * ceil(W/32) <= 2^14 pixel blocks; larger shapes return D3G_ERR_CAPACITY with a message naming the
+ * limit (d3g_image_loss_static_limits reports both limits and the array size).  All calls on a device share the one
+ * array: calls that overlap on the GPU (different streams, or a graph replay concurrent with an eager call) race on it
+ * — serialise them.  The array keeps the previous call's contents, and nothing in it has to start at zero (every word
+ * a kernel reads is written earlier in the same call).  There is no static counterpart of d3g_image_loss_backward:
+ * pass dL_dimg here to get the gradient in the same call. */
+int d3g_image_loss_static_limits(size_t* max_elements, size_t* max_blocks, size_t* scratch_bytes);
+int d3g_image_loss_static(int32_t C, int32_t H, int32_t W, const float* img, const float* gt, float w_l1,
+                          float w_ssim, float bias, float* out3, float* dL_dimg, void* stream);
 
 /* Fused multi-tensor Adam step: what `optimizer.step()` of scene/gaussian_model.py:136 and
  * scene/deform_model.py:295,337 (torch.optim.Adam, betas (0.9, 0.999), eps 1e-15, optional weight_decay, no amsgrad)
