@@ -200,8 +200,18 @@ class Workload:
             self.flat = self.grads.flat
             # MLP backward adds straight into those .grad views (no per-parameter zero-fill + AccumulateGrad add)
             self.model.deform.fused_grad_accumulation = True
+            # ... and so do the rasterizer / prepare backward kernels for the six Gaussian parameters: no `get_features`
+            # concatenation, no six AccumulateGrad adds per frame.  Their hooks no longer fire, so the early all-reduce
+            # is started by the renderer's per-frame callback instead.
+            self.grad_sinks = os.environ.get("D3G_BENCH_GRAD_SINKS", "1") == "1"
+            if self.grad_sinks:
+                renderer = pkg("renderer")
+                renderer.FUSED_GRAD_ACCUMULATION = True
+                self.grads.frames_per_exchange = max(len(self.mine), 1)
+                renderer.ON_GAUSSIAN_GRADS = self.grads.on_frame_grads if self.early else None
         else:
             self.grads = self.flat = None
+            self.grad_sinks = False
         # sync-free frames: the binning workspace is sized from the largest pair count seen so far (+ headroom) instead
         # of reading `num_rendered` back in the middle of every frame; overflow is checked where the host syncs anyway
         ras = pkg("rasterizer")
@@ -699,6 +709,9 @@ def main():
                        "loss": ("0.8*L1 + 0.2*(1-SSIM) vs fixed random images (fused CUDA loss); multi-frame batches use "
                                 "the reference's cumulative-L1 frame weights (train.py:245-250)") if cfg["train"] else None,
                        "pair_capacity": "GrowingPairCapacity: no num_rendered read-back inside a frame",
+                       "grad_accumulation": ("backward kernels add into the flat .grad views (MLP and Gaussian parameters; "
+                                             "SH coefficients read from _features_dc/_features_rest in place)"
+                                             if getattr(work, "grad_sinks", False) else "autograd AccumulateGrad"),
                        "launch": ("one CUDA-graph replay per step (frames.GraphedStep: the whole fwd+bwd step incl. the "
                                   "H2D/D2H copies of the end-to-end leg is captured once)" if graphed else
                                   "eager: every kernel launched from Python each step"),

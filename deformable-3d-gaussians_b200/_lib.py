@@ -107,7 +107,9 @@ MlpGrads = _ptr_struct("MlpGrads")
 # every symbol include/d3g.h declares; tests check the .so exports all of them
 EXPORTS = ["d3g_last_error", "d3g_version", "d3g_prof_enable", "d3g_prof_count", "d3g_prof_name", "d3g_prof_collect", "d3g_raster_geom_bytes", "d3g_raster_img_bytes",
            "d3g_raster_bin_bytes", "d3g_raster_preprocess", "d3g_raster_render", "d3g_raster_backward",
-           "d3g_mark_visible", "d3g_gaussians_prepare", "d3g_gaussians_prepare_backward", "d3g_raster_read_header", "d3g_raster_header_async", "d3g_raster_read_state", "d3g_mlp_packed_bytes",
+           "d3g_raster_preprocess_split", "d3g_raster_backward_split",
+           "d3g_mark_visible", "d3g_gaussians_prepare", "d3g_gaussians_prepare_backward",
+           "d3g_gaussians_prepare_backward_into", "d3g_raster_read_header", "d3g_raster_header_async", "d3g_raster_read_state", "d3g_mlp_packed_bytes",
            "d3g_mlp_workspace_bytes", "d3g_mlp_workspace_bytes_times", "d3g_mlp_pack_weights", "d3g_mlp_forward", "d3g_mlp_forward_times", "d3g_mlp_backward", "d3g_mlp_backward_times", "d3g_mlp_read_status", "d3g_mlp_read_masks", "d3g_mlp_sm_reserve",
            "d3g_image_loss_workspace_bytes",
            "d3g_image_loss", "d3g_image_loss_backward", "d3g_image_loss_static", "d3g_image_loss_static_limits", "d3g_adam_step", "d3g_densification_stats", "d3g_knn_mean_dist2", "d3g_knn_workspace_bytes",

@@ -71,10 +71,18 @@ __global__ void __launch_bounds__(256)
 prepare_bwd_kernel(PrepArgs a, const float* __restrict__ g_means3D, const float* __restrict__ g_opac,
                    const float* __restrict__ g_scales, const float* __restrict__ g_rots,
                    float* __restrict__ g_xyz, float* __restrict__ g_T, float* __restrict__ g_opacity,
-                   float* __restrict__ g_scaling, float* __restrict__ g_rotation) {
+                   float* __restrict__ g_scaling, float* __restrict__ g_rotation, const bool acc) {
+  // acc: the four parameter cotangents are added to what g_xyz / g_opacity / g_scaling / g_rotation hold (the
+  // parameters' .grad tensors) instead of overwriting them; each thread owns its elements, so plain read-add-write.
+  // (__fadd_rn: the sum is never contracted into the product that feeds it, so the result is bit-identical to
+  //  writing the cotangent out and letting autograd add it)
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= a.N) return;
   const size_t si = (size_t)i;
+  if (!a.is_6dof && acc && g_xyz && g_means3D) {
+#pragma unroll
+    for (int k = 0; k < 3; k++) g_xyz[3 * si + k] = __fadd_rn(g_xyz[3 * si + k], g_means3D[3 * si + k]);
+  }
   if (a.is_6dof && (g_xyz || g_T)) {
     const float x = a.xyz[3 * si], y = a.xyz[3 * si + 1], z = a.xyz[3 * si + 2];
     const float4* T = (const float4*)(a.d_xyz + 16 * si);
@@ -94,19 +102,25 @@ prepare_bwd_kernel(PrepArgs a, const float* __restrict__ g_means3D, const float*
       for (int r = 0; r < 4; r++) o[r] = make_float4(gm[r] * x, gm[r] * y, gm[r] * z, gm[r]);
     }
     if (g_xyz) {
-      g_xyz[3 * si] = gm[0] * t[0].x + gm[1] * t[1].x + gm[2] * t[2].x + gm[3] * t[3].x;
-      g_xyz[3 * si + 1] = gm[0] * t[0].y + gm[1] * t[1].y + gm[2] * t[2].y + gm[3] * t[3].y;
-      g_xyz[3 * si + 2] = gm[0] * t[0].z + gm[1] * t[1].z + gm[2] * t[2].z + gm[3] * t[3].z;
+      const float gx = gm[0] * t[0].x + gm[1] * t[1].x + gm[2] * t[2].x + gm[3] * t[3].x;
+      const float gy = gm[0] * t[0].y + gm[1] * t[1].y + gm[2] * t[2].y + gm[3] * t[3].y;
+      const float gz = gm[0] * t[0].z + gm[1] * t[1].z + gm[2] * t[2].z + gm[3] * t[3].z;
+      g_xyz[3 * si] = acc ? __fadd_rn(g_xyz[3 * si], gx) : gx;
+      g_xyz[3 * si + 1] = acc ? __fadd_rn(g_xyz[3 * si + 1], gy) : gy;
+      g_xyz[3 * si + 2] = acc ? __fadd_rn(g_xyz[3 * si + 2], gz) : gz;
     }
   }
   if (g_opacity) {
     const float s = 1.0f / (1.0f + expf(-a.opacity[si]));
-    g_opacity[si] = g_opac ? g_opac[si] * (1.0f - s) * s : 0.f;
+    const float v = g_opac ? g_opac[si] * (1.0f - s) * s : 0.f;
+    g_opacity[si] = acc ? __fadd_rn(g_opacity[si], v) : v;
   }
   if (g_scaling) {
 #pragma unroll
-    for (int k = 0; k < 3; k++)
-      g_scaling[3 * si + k] = g_scales ? g_scales[3 * si + k] * expf(a.scaling[3 * si + k]) : 0.f;
+    for (int k = 0; k < 3; k++) {
+      const float v = g_scales ? g_scales[3 * si + k] * expf(a.scaling[3 * si + k]) : 0.f;
+      g_scaling[3 * si + k] = acc ? __fadd_rn(g_scaling[3 * si + k], v) : v;
+    }
   }
   if (g_rotation) {
     float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -121,6 +135,10 @@ prepare_bwd_kernel(PrepArgs a, const float* __restrict__ g_means3D, const float*
       } else {  // clamped denominator: y = q / eps
         o = make_float4(g.x * 1e12f, g.y * 1e12f, g.z * 1e12f, g.w * 1e12f);
       }
+    }
+    if (acc) {
+      const float4 h = *(const float4*)(g_rotation + 4 * si);
+      o.x = __fadd_rn(h.x, o.x); o.y = __fadd_rn(h.y, o.y); o.z = __fadd_rn(h.z, o.z); o.w = __fadd_rn(h.w, o.w);
     }
     *(float4*)(g_rotation + 4 * si) = o;
   }
@@ -157,20 +175,41 @@ extern "C" int d3g_gaussians_prepare(int32_t N, int32_t is_6dof, const float* xy
   return 0;
 }
 
+static int prepare_backward_impl(int32_t N, int32_t is_6dof, const float* xyz, const float* d_xyz,
+                                 const float* scaling, const float* rotation, const float* opacity,
+                                 const float* g_means3D, const float* g_opacity_out, const float* g_scales_out,
+                                 const float* g_rotations_out, float* g_xyz, float* g_dxyz_6dof, float* g_opacity,
+                                 float* g_scaling, float* g_rotation, bool acc, void* stream_) {
+  PrepArgs a;
+  if (int e = fill_args(a, N, is_6dof, xyz, d_xyz, scaling, nullptr, rotation, nullptr, opacity)) return e;
+  if (N == 0) return 0;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  prepare_bwd_kernel<<<(N + 255) / 256, 256, 0, stream>>>(a, g_means3D, g_opacity_out, g_scales_out, g_rotations_out,
+                                                          g_xyz, g_dxyz_6dof, g_opacity, g_scaling, g_rotation, acc);
+  D3G_LAUNCH_CHECK(0, stream);
+  return 0;
+}
+
 extern "C" int d3g_gaussians_prepare_backward(int32_t N, int32_t is_6dof, const float* xyz, const float* d_xyz,
                                               const float* scaling, const float* rotation, const float* opacity,
                                               const float* g_means3D, const float* g_opacity_out,
                                               const float* g_scales_out, const float* g_rotations_out,
                                               float* g_xyz, float* g_dxyz_6dof, float* g_opacity,
                                               float* g_scaling, float* g_rotation, void* stream_) {
-  PrepArgs a;
-  if (int e = fill_args(a, N, is_6dof, xyz, d_xyz, scaling, nullptr, rotation, nullptr, opacity)) return e;
-  if (N == 0) return 0;
-  cudaStream_t stream = (cudaStream_t)stream_;
-  prepare_bwd_kernel<<<(N + 255) / 256, 256, 0, stream>>>(a, g_means3D, g_opacity_out, g_scales_out, g_rotations_out,
-                                                          g_xyz, g_dxyz_6dof, g_opacity, g_scaling, g_rotation);
-  D3G_LAUNCH_CHECK(0, stream);
-  return 0;
+  return prepare_backward_impl(N, is_6dof, xyz, d_xyz, scaling, rotation, opacity, g_means3D, g_opacity_out,
+                               g_scales_out, g_rotations_out, g_xyz, g_dxyz_6dof, g_opacity, g_scaling, g_rotation,
+                               false, stream_);
+}
+
+extern "C" int d3g_gaussians_prepare_backward_into(int32_t N, int32_t is_6dof, const float* xyz, const float* d_xyz,
+                                                   const float* scaling, const float* rotation, const float* opacity,
+                                                   const float* g_means3D, const float* g_opacity_out,
+                                                   const float* g_scales_out, const float* g_rotations_out,
+                                                   float* acc_xyz, float* g_dxyz_6dof, float* acc_opacity,
+                                                   float* acc_scaling, float* acc_rotation, void* stream_) {
+  return prepare_backward_impl(N, is_6dof, xyz, d_xyz, scaling, rotation, opacity, g_means3D, g_opacity_out,
+                               g_scales_out, g_rotations_out, acc_xyz, g_dxyz_6dof, acc_opacity, acc_scaling,
+                               acc_rotation, true, stream_);
 }
 
 // ------------------------------------------------------------------------------------------------

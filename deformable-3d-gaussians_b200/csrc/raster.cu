@@ -302,8 +302,27 @@ struct RasterArgs {
 // ================================================================================================
 // stage 1: preprocess — one thread per Gaussian
 // ================================================================================================
+// kSplit: the SH coefficients stay in the reference's two parameters — `shs` is _features_dc [N,1,3] and `sh_rest`
+// _features_rest [N,15,3] (scene/gaussian_model.py:111-115) — instead of their concatenation.  A warp's 32 rows of
+// sh_rest are one contiguous, 16-byte aligned run of 5760 bytes: the warp copies it to shared memory with coalesced
+// 16-byte loads and every lane then reads its own row at a 45-word stride (odd: no bank conflicts).  The colour is
+// accumulated in the same order from the same values, so it is bit-identical to the concatenated layout.
+constexpr int kShRestRow = 45;                    // floats per Gaussian in _features_rest (15 coefficients x RGB)
+constexpr int kShRestWarp = 32 * kShRestRow;      // floats per warp
+
+__device__ __forceinline__ void stage_sh_rest(float* __restrict__ dst, const float* __restrict__ src, int cnt,
+                                              int lane) {
+  const int nf = cnt * kShRestRow;
+  const float4* s4 = reinterpret_cast<const float4*>(src);
+  float4* d4 = reinterpret_cast<float4*>(dst);
+  for (int q = lane; q < (nf >> 2); q += 32) d4[q] = __ldg(s4 + q);
+  for (int e = (nf & ~3) + lane; e < nf; e += 32) dst[e] = __ldg(src + e);   // (a partial last warp)
+}
+
+template <bool kSplit>
 __global__ void __launch_bounds__(256)
 preprocess_fwd_kernel(RasterArgs a, const float* __restrict__ means3D, const float* __restrict__ shs,
+                      const float* __restrict__ sh_rest,
                       const float* __restrict__ colors_precomp, const float* __restrict__ opacities,
                       const float* __restrict__ scales, const float* __restrict__ rots,
                       const float* __restrict__ cov3D_precomp, int32_t* __restrict__ radii,
@@ -312,7 +331,8 @@ preprocess_fwd_kernel(RasterArgs a, const float* __restrict__ means3D, const flo
                       uint32_t* __restrict__ tiles_touched, uint8_t* __restrict__ clamped,
                       uint32_t* __restrict__ pair_counter) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= a.N) return;
+  const bool valid = i < a.N;
+  if (!kSplit && !valid) return;     // (kSplit: every lane stays for the warp-wide staging below)
   int radius_out = 0;
   uint32_t tiles = 0;
   float2 m2 = make_float2(0.f, 0.f);
@@ -321,8 +341,11 @@ preprocess_fwd_kernel(RasterArgs a, const float* __restrict__ means3D, const flo
   float cov6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   uint8_t clamp_bits = 0;
   bool visible = false;
+  float p[3] = {0.f, 0.f, 0.f};
+  float conx = 0.f, cony = 0.f, conz = 0.f, px = 0.f, py = 0.f, depth = 0.f;
   do {
-    float p[3] = {means3D[3 * i], means3D[3 * i + 1], means3D[3 * i + 2]};
+    if (kSplit && !valid) break;
+    p[0] = means3D[3 * (size_t)i]; p[1] = means3D[3 * (size_t)i + 1]; p[2] = means3D[3 * (size_t)i + 2];
     float pv[3], ph[4];
     xform4x3(a.view, p, pv);
     if (!(pv[2] > 0.2f)) break;
@@ -344,17 +367,33 @@ preprocess_fwd_kernel(RasterArgs a, const float* __restrict__ means3D, const flo
     float det = ff(c2.A, c2.C, -fm(c2.B, c2.B));
     if (det == 0.0f) break;
     float det_inv = fdv(1.0f, det);
-    float conx = fm(c2.C, det_inv), cony = fm(-c2.B, det_inv), conz = fm(c2.A, det_inv);
+    conx = fm(c2.C, det_inv); cony = fm(-c2.B, det_inv); conz = fm(c2.A, det_inv);
     float mid = fm(0.5f, fa(c2.A, c2.C));
     float disc = cmax(0.1f, ff(mid, mid, -det));
     float sq = fsq(disc);
     float l1 = fa(mid, sq), l2 = fs(mid, sq);
     float rad_f = ceilf(fm(3.0f, fsq(cmax(l1, l2))));
     int my_radius = __float2int_rz(rad_f);
-    float px = ndc2pix(ppx, a.W), py = ndc2pix(ppy, a.H);
+    px = ndc2pix(ppx, a.W); py = ndc2pix(ppy, a.H);
     int mnx, mny, mxx, mxy;
     get_rect(px, py, my_radius, a.gx, a.gy, mnx, mny, mxx, mxy);
     if ((mxx - mnx) * (mxy - mny) == 0) break;
+#pragma unroll
+    for (int k = 0; k < 6; k++) cov6[k] = c6[k];
+    radius_out = my_radius;
+    depth = pv[2];
+    tiles = (uint32_t)((mxx - mnx) * (mxy - mny));
+    visible = true;
+  } while (0);
+  __shared__ __align__(16) float s_rest[kSplit ? 8 : 1][kSplit ? kShRestWarp : 4];
+  if (kSplit) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int i0 = i - lane, cnt = min(32, a.N - i0);
+    if (__any_sync(0xffffffffu, visible)) stage_sh_rest(s_rest[warp], sh_rest + (size_t)i0 * kShRestRow, cnt, lane);
+    __syncwarp();
+    if (!valid) return;
+  }
+  if (visible) {
     float rgb[3];
     if (colors_precomp) {
       rgb[0] = colors_precomp[3 * (size_t)i];
@@ -367,18 +406,25 @@ preprocess_fwd_kernel(RasterArgs a, const float* __restrict__ means3D, const flo
       float b[16];
       sh_basis(a.sh_degree, d, b);
       int nb = (a.sh_degree + 1) * (a.sh_degree + 1);
-      const float* sh = shs + (size_t)i * a.M * 3;
+      const float* sh = shs + (size_t)i * (kSplit ? 1 : a.M) * 3;
       float r0, r1, r2;
-      if (a.M == 16 && (((uintptr_t)shs) & 15) == 0) {
-        // the usual [N,16,3] layout: 192 contiguous, 16-byte aligned bytes per Gaussian -> up to twelve 16-byte loads
-        // issued together instead of 48 dependent scalar loads; same FMA order, so the colours stay bit-identical
+      if (kSplit || (a.M == 16 && (((uintptr_t)shs) & 15) == 0)) {
         float v[48];
-        const float4* s4 = reinterpret_cast<const float4*>(sh);
+        if (kSplit) {
+          const float* row = &s_rest[threadIdx.x >> 5][(threadIdx.x & 31) * kShRestRow];
+          v[0] = sh[0]; v[1] = sh[1]; v[2] = sh[2];
 #pragma unroll
-        for (int q = 0; q < 12; q++) {
-          float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (4 * q < 3 * nb) t = s4[q];
-          v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
+          for (int e = 0; e < kShRestRow; e++) v[3 + e] = (e < 3 * (nb - 1)) ? row[e] : 0.f;
+        } else {
+          // the usual [N,16,3] layout: 192 contiguous, 16-byte aligned bytes per Gaussian -> up to twelve 16-byte loads
+          // issued together instead of 48 dependent scalar loads; same FMA order, so the colours stay bit-identical
+          const float4* s4 = reinterpret_cast<const float4*>(sh);
+#pragma unroll
+          for (int q = 0; q < 12; q++) {
+            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (4 * q < 3 * nb) t = s4[q];
+            v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
+          }
         }
         r0 = fm(b[0], v[0]); r1 = fm(b[0], v[1]); r2 = fm(b[0], v[2]);
 #pragma unroll
@@ -401,15 +447,10 @@ preprocess_fwd_kernel(RasterArgs a, const float* __restrict__ means3D, const flo
       clamp_bits = (r0 < 0.0f ? 1 : 0) | (r1 < 0.0f ? 2 : 0) | (r2 < 0.0f ? 4 : 0);
       rgb[0] = cmax(r0, 0.0f); rgb[1] = cmax(r1, 0.0f); rgb[2] = cmax(r2, 0.0f);
     }
-#pragma unroll
-    for (int k = 0; k < 6; k++) cov6[k] = c6[k];
-    radius_out = my_radius;
     m2 = make_float2(px, py);
     co = make_float4(conx, cony, conz, opacities[i]);
-    cd = make_float4(rgb[0], rgb[1], rgb[2], pv[2]);
-    tiles = (uint32_t)((mxx - mnx) * (mxy - mny));
-    visible = true;
-  } while (0);
+    cd = make_float4(rgb[0], rgb[1], rgb[2], depth);
+  }
   if (!visible) clamp_bits = 0;
   radii[i] = radius_out;
   means2D[i] = m2;
@@ -1032,21 +1073,37 @@ render_bwd_kernel(int H, int W, int gx, const float* __restrict__ bg,
 // ================================================================================================
 // stage 5: preprocess backward (cov2D bwd + mean/colour/cov3D chain) — one thread per Gaussian
 // ================================================================================================
+// kSplit (see preprocess_fwd_kernel): `shs` / `sh_rest` are _features_dc / _features_rest, and dL/dSH is ADDED to
+// `dL_dsh` ([N,1,3], the .grad of _features_dc) and `dL_dsh_rest` ([N,15,3], the .grad of _features_rest): the warp
+// stages its 32 gradient rows in the shared-memory block the coefficients were read from and adds the contiguous
+// 5760-byte run to global memory with coalesced 16-byte read-add-writes.
+template <bool kSplit>
 __global__ void __launch_bounds__(256)
 preprocess_bwd_kernel(RasterArgs a, const float* __restrict__ means3D, const float* __restrict__ shs,
+                      const float* __restrict__ sh_rest,
                       const float* __restrict__ colors_precomp, const float* __restrict__ scales,
                       const float* __restrict__ rots, const int32_t* __restrict__ radii,
                       const float* __restrict__ cov3D, const uint8_t* __restrict__ clamped,
                       const float4* __restrict__ acc_mean, const float4* __restrict__ acc_conic,
                       const float4* __restrict__ acc_color, float* __restrict__ dL_dmeans3D,
                       float* __restrict__ dL_dmeans2D, float* __restrict__ dL_dmeans2D_densify,
-                      float* __restrict__ dL_dsh, float* __restrict__ dL_dcolors_precomp,
+                      float* __restrict__ dL_dsh, float* __restrict__ dL_dsh_rest,
+                      float* __restrict__ dL_dcolors_precomp,
                       float* __restrict__ dL_dopacities, float* __restrict__ dL_dscales,
                       float* __restrict__ dL_drots, float* __restrict__ dL_dcov3D) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= a.N) return;
+  const bool valid = i < a.N;
+  if (!kSplit && !valid) return;
+  bool vis = valid && radii[i] > 0;
+  __shared__ __align__(16) float s_rest[kSplit ? 8 : 1][kSplit ? kShRestWarp : 4];
+  if (kSplit) {   // every lane of the warp takes part in the staging, then the lanes past N leave
+    const int lane0 = threadIdx.x & 31;
+    const int i0 = i - lane0, cnt0 = min(32, a.N - i0);
+    if (__any_sync(0xffffffffu, vis)) stage_sh_rest(s_rest[threadIdx.x >> 5], sh_rest + (size_t)i0 * kShRestRow, cnt0, lane0);
+    __syncwarp();
+    if (!valid) return;
+  }
   size_t si = (size_t)i;
-  bool vis = radii[i] > 0;
   float4 gm = vis ? acc_mean[i] : make_float4(0, 0, 0, 0);
   float4 gc = vis ? acc_conic[i] : make_float4(0, 0, 0, 0);
   float4 gcol = vis ? acc_color[i] : make_float4(0, 0, 0, 0);
@@ -1149,16 +1206,23 @@ preprocess_bwd_kernel(RasterArgs a, const float* __restrict__ means3D, const flo
       sh_basis(a.sh_degree, d, b);
       uint8_t cb = clamped[i];
       float dRGB[3] = {(cb & 1) ? 0.f : gcol.x, (cb & 2) ? 0.f : gcol.y, (cb & 4) ? 0.f : gcol.z};
-      const float* sh = shs + si * a.M * 3;
+      const float* sh = shs + si * (kSplit ? 1 : a.M) * 3;
       float sdot[16];
-      if (a.M == 16 && (((uintptr_t)shs) & 15) == 0) {   // vector loads of the 192-byte coefficient block
+      if (kSplit || (a.M == 16 && (((uintptr_t)shs) & 15) == 0)) {
         float v[48];
-        const float4* s4 = reinterpret_cast<const float4*>(sh);
+        if (kSplit) {
+          const float* row = &s_rest[threadIdx.x >> 5][(threadIdx.x & 31) * kShRestRow];
+          v[0] = sh[0]; v[1] = sh[1]; v[2] = sh[2];
 #pragma unroll
-        for (int q = 0; q < 12; q++) {
-          float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (4 * q < 3 * nb) t = s4[q];
-          v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
+          for (int e = 0; e < kShRestRow; e++) v[3 + e] = (e < 3 * (nb - 1)) ? row[e] : 0.f;
+        } else {   // vector loads of the 192-byte coefficient block
+          const float4* s4 = reinterpret_cast<const float4*>(sh);
+#pragma unroll
+          for (int q = 0; q < 12; q++) {
+            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (4 * q < 3 * nb) t = s4[q];
+            v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
+          }
         }
 #pragma unroll
         for (int k = 0; k < 16; k++) {
@@ -1251,7 +1315,34 @@ preprocess_bwd_kernel(RasterArgs a, const float* __restrict__ means3D, const flo
 #pragma unroll
     for (int k = 0; k < 6; k++) dL_dcov3D[6 * si + k] = dcov[k];
   }
-  if (dL_dsh) {
+  if (kSplit) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int i0 = i - lane;
+    const int cnt = min(32, a.N - i0);
+    const unsigned mask = cnt >= 32 ? 0xffffffffu : ((1u << cnt) - 1u);
+    // (every lane has consumed its coefficient row — it is only ever read by its own lane — so the block is free)
+    if (!__any_sync(mask, vis)) return;   // a warp of culled Gaussians adds nothing
+    if (vis) {
+#pragma unroll
+      for (int c = 0; c < 3; c++)   // (no contraction of the product into the sum: bit-identical to autograd's add)
+        dL_dsh[3 * si + c] = __fadd_rn(dL_dsh[3 * si + c], __fmul_rn(shb[0], shg[c]));
+    }
+    float* row = &s_rest[warp][lane * kShRestRow];
+#pragma unroll
+    for (int e = 0; e < kShRestRow; e++) row[e] = shb[1 + e / 3] * shg[e % 3];
+    __syncwarp(mask);
+    const int nf = cnt * kShRestRow;
+    float* out = dL_dsh_rest + (size_t)i0 * kShRestRow;
+    float4* o4 = reinterpret_cast<float4*>(out);
+    const float4* s4 = reinterpret_cast<const float4*>(s_rest[warp]);
+    for (int q = lane; q < (nf >> 2); q += cnt) {     // only lanes 0..cnt-1 exist in a partial warp
+      float4 g = o4[q];
+      const float4 t = s4[q];
+      g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
+      o4[q] = g;
+    }
+    for (int e = (nf & ~3) + lane; e < nf; e += cnt) out[e] += s_rest[warp][e];
+  } else if (dL_dsh) {
     __shared__ float s_sh[256 / 32][32][25];   // one 24-float slice of 32 Gaussians per warp (+1 pad: no bank conflicts)
     // the lanes of this warp that hold a Gaussian (the last warp of the grid may be partial); named explicitly —
     // __activemask() would only report the lanes that happen to have reconverged after the branches above
@@ -1334,11 +1425,14 @@ int d3g_raster_bin_bytes(uint64_t cap, size_t* bytes) {
   return 0;
 }
 
-int d3g_raster_preprocess(const d3g_raster_settings* s, int32_t N, const float* means3D,
-                          const float* shs, int32_t M, const float* colors_precomp,
-                          const float* opacities, const float* scales, const float* rotations,
-                          const float* cov3D_precomp, void* geom, int32_t* radii,
-                          uint32_t* num_rendered_host, void* stream_) {
+}  // extern "C"
+
+// sh_rest != NULL: `shs` is _features_dc [N,1,3] and `sh_rest` _features_rest [N,15,3] (the *_split entry points)
+static int raster_preprocess_impl(const d3g_raster_settings* s, int32_t N, const float* means3D,
+                                  const float* shs, const float* sh_rest, int32_t M, const float* colors_precomp,
+                                  const float* opacities, const float* scales, const float* rotations,
+                                  const float* cov3D_precomp, void* geom, int32_t* radii,
+                                  uint32_t* num_rendered_host, void* stream_) {
   if (int e = check_settings(s)) return e;
   cudaStream_t stream = (cudaStream_t)stream_;
   // (empty tensors have NULL data pointers, so the either/or checks only apply when N > 0; the Python
@@ -1359,9 +1453,14 @@ int d3g_raster_preprocess(const d3g_raster_settings* s, int32_t N, const float* 
     { ProfScope _p(PROF_PREPROCESS_FWD, stream);
     const bool tile_mode = a.binning_mode == 0;
     if (tile_mode) D3G_CUDA_TRY(cudaMemsetAsync(g.header, 0, 8, stream));
-    preprocess_fwd_kernel<<<(N + 255) / 256, 256, 0, stream>>>(
-        a, means3D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp, radii, g.means2D,
-        g.conic_opacity, g.rgbd, g.cov3D, g.tiles_touched, g.clamped, tile_mode ? g.header : nullptr);
+    if (sh_rest)
+      preprocess_fwd_kernel<true><<<(N + 255) / 256, 256, 0, stream>>>(
+          a, means3D, shs, sh_rest, colors_precomp, opacities, scales, rotations, cov3D_precomp, radii, g.means2D,
+          g.conic_opacity, g.rgbd, g.cov3D, g.tiles_touched, g.clamped, tile_mode ? g.header : nullptr);
+    else
+      preprocess_fwd_kernel<false><<<(N + 255) / 256, 256, 0, stream>>>(
+          a, means3D, shs, nullptr, colors_precomp, opacities, scales, rotations, cov3D_precomp, radii, g.means2D,
+          g.conic_opacity, g.rgbd, g.cov3D, g.tiles_touched, g.clamped, tile_mode ? g.header : nullptr);
     D3G_LAUNCH_CHECK(s->debug, stream); }
     if (a.binning_mode != 0) {   // the reference's own scheme needs the per-Gaussian offsets
       size_t tb = g.scan_temp_bytes;
@@ -1377,6 +1476,34 @@ int d3g_raster_preprocess(const d3g_raster_settings* s, int32_t N, const float* 
   if (num_rendered_host)
     D3G_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, g.header, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
   return 0;
+}
+
+static int check_split(int32_t N, const float* dc, const float* rest, int32_t M) {
+  if (M != 16) return set_err(D3G_ERR_UNSUPPORTED, "split SH features need sh_coeffs = 16 (max_sh_degree 3)");
+  if (N > 0 && (!dc || !rest)) return set_err(D3G_ERR_INVALID, "features_dc / features_rest is NULL");
+  if (((uintptr_t)rest) & 15) return set_err(D3G_ERR_INVALID, "features_rest must be 16-byte aligned");
+  return 0;
+}
+
+extern "C" {
+
+int d3g_raster_preprocess(const d3g_raster_settings* s, int32_t N, const float* means3D,
+                          const float* shs, int32_t M, const float* colors_precomp,
+                          const float* opacities, const float* scales, const float* rotations,
+                          const float* cov3D_precomp, void* geom, int32_t* radii,
+                          uint32_t* num_rendered_host, void* stream_) {
+  return raster_preprocess_impl(s, N, means3D, shs, nullptr, M, colors_precomp, opacities, scales, rotations,
+                                cov3D_precomp, geom, radii, num_rendered_host, stream_);
+}
+
+int d3g_raster_preprocess_split(const d3g_raster_settings* s, int32_t N, const float* means3D,
+                                const float* features_dc, const float* features_rest, int32_t M,
+                                const float* opacities, const float* scales, const float* rotations,
+                                const float* cov3D_precomp, void* geom, int32_t* radii,
+                                uint32_t* num_rendered_host, void* stream_) {
+  if (int e = check_split(N, features_dc, features_rest, M)) return e;
+  return raster_preprocess_impl(s, N, means3D, features_dc, N > 0 ? features_rest : nullptr, M, nullptr, opacities,
+                                scales, rotations, cov3D_precomp, geom, radii, num_rendered_host, stream_);
 }
 
 int d3g_raster_render(const d3g_raster_settings* s, int32_t N, uint64_t cap, void* geom, void* bin,
@@ -1443,14 +1570,17 @@ int d3g_raster_render(const d3g_raster_settings* s, int32_t N, uint64_t cap, voi
   return 0;
 }
 
-int d3g_raster_backward(const d3g_raster_settings* s, int32_t N, uint64_t cap, const float* means3D,
-                        const float* shs, int32_t M, const float* colors_precomp, const float* scales,
-                        const float* rotations, const float* cov3D_precomp, const int32_t* radii,
-                        void* geom, void* bin, void* img, const float* dL_dcolor, const float* dL_ddepth,
-                        float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dmeans2D_densify,
-                        float* dL_dshs, float* dL_dcolors_precomp, float* dL_dopacities,
-                        float* dL_dscales, float* dL_drotations, float* dL_dcov3D_precomp,
-                        void* stream_) {
+}  // extern "C"
+
+// sh_rest != NULL: split SH features; dL_dshs / dL_dsh_rest are then the accumulating .grad tensors of the two parameters
+static int raster_backward_impl(const d3g_raster_settings* s, int32_t N, uint64_t cap, const float* means3D,
+                                const float* shs, const float* sh_rest, int32_t M, const float* colors_precomp,
+                                const float* scales, const float* rotations, const float* cov3D_precomp,
+                                const int32_t* radii, void* geom, void* bin, void* img, const float* dL_dcolor,
+                                const float* dL_ddepth, float* dL_dmeans3D, float* dL_dmeans2D,
+                                float* dL_dmeans2D_densify, float* dL_dshs, float* dL_dsh_rest,
+                                float* dL_dcolors_precomp, float* dL_dopacities, float* dL_dscales,
+                                float* dL_drotations, float* dL_dcov3D_precomp, void* stream_) {
   if (int e = check_settings(s)) return e;
   cudaStream_t stream = (cudaStream_t)stream_;
   if (!geom || !img || (cap > 0 && !bin) || !dL_dcolor) return set_err(D3G_ERR_INVALID, "NULL workspace/cotangent");
@@ -1479,12 +1609,52 @@ int d3g_raster_backward(const d3g_raster_settings* s, int32_t N, uint64_t cap, c
     D3G_LAUNCH_CHECK(s->debug, stream); }
   }
   { ProfScope _p(PROF_PREPROCESS_BWD, stream);
-    preprocess_bwd_kernel<<<(N + 255) / 256, 256, 0, stream>>>(
-      a, means3D, shs, colors_precomp, scales, rotations, radii, g.cov3D, g.clamped, g.acc_mean, g.acc_conic,
-      g.acc_color, dL_dmeans3D, dL_dmeans2D, dL_dmeans2D_densify, dL_dshs, dL_dcolors_precomp, dL_dopacities,
-      dL_dscales, dL_drotations, dL_dcov3D_precomp);
+    if (sh_rest)
+      preprocess_bwd_kernel<true><<<(N + 255) / 256, 256, 0, stream>>>(
+        a, means3D, shs, sh_rest, colors_precomp, scales, rotations, radii, g.cov3D, g.clamped, g.acc_mean, g.acc_conic,
+        g.acc_color, dL_dmeans3D, dL_dmeans2D, dL_dmeans2D_densify, dL_dshs, dL_dsh_rest, dL_dcolors_precomp,
+        dL_dopacities, dL_dscales, dL_drotations, dL_dcov3D_precomp);
+    else
+      preprocess_bwd_kernel<false><<<(N + 255) / 256, 256, 0, stream>>>(
+        a, means3D, shs, nullptr, colors_precomp, scales, rotations, radii, g.cov3D, g.clamped, g.acc_mean, g.acc_conic,
+        g.acc_color, dL_dmeans3D, dL_dmeans2D, dL_dmeans2D_densify, dL_dshs, nullptr, dL_dcolors_precomp,
+        dL_dopacities, dL_dscales, dL_drotations, dL_dcov3D_precomp);
   D3G_LAUNCH_CHECK(s->debug, stream); }
   return 0;
+}
+
+extern "C" {
+
+int d3g_raster_backward(const d3g_raster_settings* s, int32_t N, uint64_t cap, const float* means3D,
+                        const float* shs, int32_t M, const float* colors_precomp, const float* scales,
+                        const float* rotations, const float* cov3D_precomp, const int32_t* radii,
+                        void* geom, void* bin, void* img, const float* dL_dcolor, const float* dL_ddepth,
+                        float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dmeans2D_densify,
+                        float* dL_dshs, float* dL_dcolors_precomp, float* dL_dopacities,
+                        float* dL_dscales, float* dL_drotations, float* dL_dcov3D_precomp,
+                        void* stream_) {
+  return raster_backward_impl(s, N, cap, means3D, shs, nullptr, M, colors_precomp, scales, rotations, cov3D_precomp,
+                              radii, geom, bin, img, dL_dcolor, dL_ddepth, dL_dmeans3D, dL_dmeans2D,
+                              dL_dmeans2D_densify, dL_dshs, nullptr, dL_dcolors_precomp, dL_dopacities, dL_dscales,
+                              dL_drotations, dL_dcov3D_precomp, stream_);
+}
+
+int d3g_raster_backward_split(const d3g_raster_settings* s, int32_t N, uint64_t cap, const float* means3D,
+                              const float* features_dc, const float* features_rest, int32_t M,
+                              const float* scales, const float* rotations, const float* cov3D_precomp,
+                              const int32_t* radii, void* geom, void* bin, void* img, const float* dL_dcolor,
+                              const float* dL_ddepth, float* dL_dmeans3D, float* dL_dmeans2D,
+                              float* dL_dmeans2D_densify, float* grad_features_dc, float* grad_features_rest,
+                              float* dL_dopacities, float* dL_dscales, float* dL_drotations,
+                              float* dL_dcov3D_precomp, void* stream_) {
+  if (int e = check_split(N, features_dc, features_rest, M)) return e;
+  if (N > 0 && (!grad_features_dc || !grad_features_rest))
+    return set_err(D3G_ERR_INVALID, "grad_features_dc / grad_features_rest is NULL");
+  if (((uintptr_t)grad_features_rest) & 15) return set_err(D3G_ERR_INVALID, "grad_features_rest must be 16-byte aligned");
+  return raster_backward_impl(s, N, cap, means3D, features_dc, features_rest, M, nullptr, scales, rotations,
+                              cov3D_precomp, radii, geom, bin, img, dL_dcolor, dL_ddepth, dL_dmeans3D, dL_dmeans2D,
+                              dL_dmeans2D_densify, grad_features_dc, grad_features_rest, nullptr, dL_dopacities,
+                              dL_dscales, dL_drotations, dL_dcov3D_precomp, stream_);
 }
 
 int d3g_mark_visible(int32_t N, const float* means3D, const float* viewmatrix, uint8_t* present,

@@ -88,6 +88,10 @@ class FlatGrads:
                 self.early_len = o
         self._early_n, self._seen, self._work, self._group = int(early), 0, None, None
         self.frames_per_reduce = 1  # local frames whose backward passes accumulate before one exchange
+        # renderer.FUSED_GRAD_ACCUMULATION adds the Gaussian gradients inside the kernels (no AccumulateGrad, so no
+        # hook): render() then reports every finished frame through on_frame_grads(); frames rendered per exchange
+        self.frames_per_exchange = 1
+        self._frames_seen = 0
         if early:
             for p in self.params[:early]:
                 p.register_post_accumulate_grad_hook(self._on_grad)
@@ -96,10 +100,22 @@ class FlatGrads:
         self._seen += 1
         if self._seen == self._early_n * self.frames_per_reduce:
             self._seen = 0
-            import torch.distributed as dist
-            if dist.is_available() and dist.is_initialized() and dist.get_world_size(self._group) > 1:
-                self._work = dist.all_reduce(self.flat[:self.early_len], op=dist.ReduceOp.SUM, group=self._group,
-                                             async_op=True)
+            self._reduce_early()
+
+    def on_frame_grads(self):
+        """renderer.ON_GAUSSIAN_GRADS callback: one frame's Gaussian-parameter gradients are complete in `flat`."""
+        if not self._early_n:
+            return
+        self._frames_seen += 1
+        if self._frames_seen == self.frames_per_exchange:
+            self._frames_seen = 0
+            self._reduce_early()
+
+    def _reduce_early(self):
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(self._group) > 1:
+            self._work = dist.all_reduce(self.flat[:self.early_len], op=dist.ReduceOp.SUM, group=self._group,
+                                         async_op=True)
 
     def zero(self):
         self.flat.zero_()

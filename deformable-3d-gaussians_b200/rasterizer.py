@@ -180,8 +180,9 @@ class RasterState:
         return out
 
 
-def rasterize_forward(rs, means3D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp):
-    """Forward through the C ABI. Returns (color, radii, depth, RasterState)."""
+def rasterize_forward(rs, means3D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp, sh_split=None):
+    """Forward through the C ABI. Returns (color, radii, depth, RasterState).  sh_split = (features_dc [N,1,3],
+    features_rest [N,15,3]) replaces `shs` by the two tensors it would be concatenated from."""
     dev = means3D.device
     if dev.type != "cuda":
         raise RuntimeError("GaussianRasterizer: tensors must live on a CUDA device (there is no CPU path)")
@@ -201,11 +202,18 @@ def rasterize_forward(rs, means3D, shs, colors_precomp, opacities, scales, rotat
         depth = torch.empty(1, H, W, dtype=torch.float32, device=dev)
         policy = PAIR_CAPACITY_POLICY
         host = None if policy is not None else _pinned_u32(dev)
-        _lib.check(lib.d3g_raster_preprocess(C.byref(s), N, _lib.ptr(means3D), _lib.ptr(shs), M,
-                                             _lib.ptr(colors_precomp), _lib.ptr(opacities), _lib.ptr(scales),
-                                             _lib.ptr(rotations), _lib.ptr(cov3D_precomp), _lib.ptr(geom),
-                                             _lib.ptr(radii), C.c_void_p(0 if host is None else host.data_ptr()),
-                                             C.c_void_p(stream)))
+        if sh_split is not None:
+            _lib.check(lib.d3g_raster_preprocess_split(
+                C.byref(s), N, _lib.ptr(means3D), _lib.ptr(sh_split[0]), _lib.ptr(sh_split[1]),
+                int(sh_split[0].shape[1] + sh_split[1].shape[1]), _lib.ptr(opacities), _lib.ptr(scales),
+                _lib.ptr(rotations), _lib.ptr(cov3D_precomp), _lib.ptr(geom), _lib.ptr(radii),
+                C.c_void_p(0 if host is None else host.data_ptr()), C.c_void_p(stream)))
+        else:
+            _lib.check(lib.d3g_raster_preprocess(C.byref(s), N, _lib.ptr(means3D), _lib.ptr(shs), M,
+                                                 _lib.ptr(colors_precomp), _lib.ptr(opacities), _lib.ptr(scales),
+                                                 _lib.ptr(rotations), _lib.ptr(cov3D_precomp), _lib.ptr(geom),
+                                                 _lib.ptr(radii), C.c_void_p(0 if host is None else host.data_ptr()),
+                                                 C.c_void_p(stream)))
         cap = None if policy is None else policy(N, H, W)
         if cap is None:
             if host is None:
@@ -233,13 +241,18 @@ def rasterize_forward(rs, means3D, shs, colors_precomp, opacities, scales, rotat
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, means2D_densify, sh, colors_precomp, opacities, scales, rotations,
-                cov3Ds_precomp, raster_settings):
+                cov3Ds_precomp, raster_settings, sh_split=None):
+        # sh_split = (features_dc, features_rest, grad_dc, grad_rest): the SH coefficients are read from the two
+        # parameters in place and their gradients are ADDED to the two .grad tensors by backward (render() sets
+        # this up under renderer.FUSED_GRAD_ACCUMULATION); `sh` and `colors_precomp` are then None
         means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp = map(
             _f32c, (means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp))
         color, radii, depth, state = rasterize_forward(raster_settings, means3D, sh, colors_precomp, opacities,
-                                                       scales, rotations, cov3Ds_precomp)
+                                                       scales, rotations, cov3Ds_precomp,
+                                                       None if sh_split is None else sh_split[:2])
         ctx.raster_settings = raster_settings
         ctx.state = state
+        ctx.sh_split = sh_split
         ctx.has = (sh is not None, colors_precomp is not None, scales is not None, cov3Ds_precomp is not None)
         ctx.save_for_backward(means3D, sh, colors_precomp, scales, rotations, cov3Ds_precomp, radii)
         ctx.mark_non_differentiable(radii)
@@ -272,19 +285,29 @@ class _RasterizeGaussians(torch.autograd.Function):
         g_rots = new(N, 4) if rotations is not None else None
         g_cov = new(N, 6) if cov3Ds_precomp is not None else None
         stream = torch.cuda.current_stream().cuda_stream
+        if ctx.sh_split is not None:
+            dc, rest, grad_dc, grad_rest = ctx.sh_split
+            _lib.check(lib.d3g_raster_backward_split(
+                C.byref(s), N, C.c_uint64(st.cap), _lib.ptr(means3D), _lib.ptr(dc), _lib.ptr(rest),
+                int(dc.shape[1] + rest.shape[1]), _lib.ptr(scales), _lib.ptr(rotations), _lib.ptr(cov3Ds_precomp),
+                _lib.ptr(radii), _lib.ptr(st.geom), _lib.ptr(st.bin), _lib.ptr(st.img), _lib.ptr(grad_color),
+                _lib.ptr(grad_depth), _lib.ptr(g_means3D), _lib.ptr(g_means2D), _lib.ptr(g_densify),
+                _lib.ptr(grad_dc), _lib.ptr(grad_rest), _lib.ptr(g_opac), _lib.ptr(g_scales), _lib.ptr(g_rots),
+                _lib.ptr(g_cov), C.c_void_p(stream)))
+            return (g_means3D, g_means2D, g_densify, None, None, g_opac, g_scales, g_rots, g_cov, None, None)
         _lib.check(lib.d3g_raster_backward(
             C.byref(s), N, C.c_uint64(st.cap), _lib.ptr(means3D), _lib.ptr(sh), M, _lib.ptr(colors_precomp),
             _lib.ptr(scales), _lib.ptr(rotations), _lib.ptr(cov3Ds_precomp), _lib.ptr(radii), _lib.ptr(st.geom),
             _lib.ptr(st.bin), _lib.ptr(st.img), _lib.ptr(grad_color), _lib.ptr(grad_depth), _lib.ptr(g_means3D),
             _lib.ptr(g_means2D), _lib.ptr(g_densify), _lib.ptr(g_sh), _lib.ptr(g_colors), _lib.ptr(g_opac),
             _lib.ptr(g_scales), _lib.ptr(g_rots), _lib.ptr(g_cov), C.c_void_p(stream)))
-        return (g_means3D, g_means2D, g_densify, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov, None)
+        return (g_means3D, g_means2D, g_densify, g_sh, g_colors, g_opac, g_scales, g_rots, g_cov, None, None)
 
 
 def rasterize_gaussians(means3D, means2D, means2D_densify, sh, colors_precomp, opacities, scales, rotations,
-                        cov3Ds_precomp, raster_settings):
+                        cov3Ds_precomp, raster_settings, sh_split=None):
     return _RasterizeGaussians.apply(means3D, means2D, means2D_densify, sh, colors_precomp, opacities, scales,
-                                     rotations, cov3Ds_precomp, raster_settings)
+                                     rotations, cov3Ds_precomp, raster_settings, sh_split)
 
 
 class GaussianRasterizer(nn.Module):

@@ -10,12 +10,25 @@ import math
 import torch
 
 from . import _lib
-from .rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+from .rasterizer import GaussianRasterizationSettings, GaussianRasterizer, rasterize_gaussians
 
 # render() replaces the per-frame elementwise torch launches (parameter activations + deformation deltas)
 # by one fused kernel each way when `pc` exposes the reference GaussianModel's raw parameters and its
 # stock activation functions (scene/gaussian_model.py:58-78).  Set to False to force the torch-op path.
 FUSED_PREPARE = True
+
+# Opt-in, like DeformNetwork.fused_grad_accumulation: with the fused prepare path and a `pc` whose six raw parameters
+# (_xyz, _features_dc, _features_rest, _scaling, _rotation, _opacity) already hold contiguous fp32 .grad tensors,
+# backward ADDS their gradients straight into those tensors — the kernels that produce them do the read-add-write —
+# and autograd receives None for them: no per-parameter AccumulateGrad add launch (six per frame), and the SH
+# coefficients are read from _features_dc / _features_rest in place instead of through `pc.get_features`' 19 MB
+# concatenation (and its split + strided adds in backward).  Only valid with loss.backward()-style accumulation
+# into .grad (not torch.autograd.grad), exactly like the MLP flag.
+FUSED_GRAD_ACCUMULATION = False
+# Optional callable, invoked (with no arguments) from backward each time ONE frame's Gaussian-parameter gradients
+# have all been added under FUSED_GRAD_ACCUMULATION — no post-accumulate-grad hooks fire on that path
+# (frames.FlatGrads uses it to start its early all-reduce).
+ON_GAUSSIAN_GRADS = None
 
 
 class _PrepareGaussians(torch.autograd.Function):
@@ -23,10 +36,14 @@ class _PrepareGaussians(torch.autograd.Function):
     rotations) exactly as gaussian_renderer/__init__.py:69-97 computes them, through d3g_gaussians_prepare."""
 
     @staticmethod
-    def forward(ctx, xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity, is_6dof):
+    def forward(ctx, xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity, is_6dof, sinks=None):
+        # sinks = (xyz.grad, scaling.grad, rotation.grad, opacity.grad) under FUSED_GRAD_ACCUMULATION: backward adds
+        # the four parameter gradients into them and hands autograd None
         with torch.cuda.device(xyz.device):
-            return _PrepareGaussians._forward(ctx, xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity,
-                                              is_6dof)
+            out = _PrepareGaussians._forward(ctx, xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity,
+                                             is_6dof)
+        ctx.sinks = sinks
+        return out
 
     @staticmethod
     def _forward(ctx, xyz, d_xyz, scaling, d_scaling, rotation, d_rotation, opacity, is_6dof):
@@ -61,6 +78,21 @@ class _PrepareGaussians(torch.autograd.Function):
         need = ctx.needs_input_grad
         new = lambda *shape: torch.empty(*shape, dtype=torch.float32, device=dev)
         six = ctx.is_6dof
+        if ctx.sinks is not None:
+            acc_xyz, acc_scaling, acc_rotation, acc_opacity = ctx.sinks
+            g_T = new(N, 4, 4) if (six and need[1]) else None
+            stream = torch.cuda.current_stream().cuda_stream
+            _lib.check(lib.d3g_gaussians_prepare_backward_into(
+                N, int(six), _lib.ptr(xyz), _lib.ptr(d_xyz), _lib.ptr(scaling), _lib.ptr(rotation), _lib.ptr(opacity),
+                _lib.ptr(g_means), _lib.ptr(g_opac), _lib.ptr(g_scales), _lib.ptr(g_rots), _lib.ptr(acc_xyz),
+                _lib.ptr(g_T), _lib.ptr(acc_opacity), _lib.ptr(acc_scaling), _lib.ptr(acc_rotation),
+                C.c_void_p(stream)))
+            if not six:
+                g_T = g_means if need[1] else None
+            if ON_GAUSSIAN_GRADS is not None:
+                ON_GAUSSIAN_GRADS()
+            return (None, g_T, None, g_scales if need[3] else None, None, g_rots if need[5] else None, None, None,
+                    None)
         g_xyz = new(N, 3) if (six and need[0]) else None
         g_T = new(N, 4, 4) if (six and need[1]) else None
         g_scaling = new(N, 3) if need[2] else None
@@ -75,7 +107,7 @@ class _PrepareGaussians(torch.autograd.Function):
             g_xyz = g_means if need[0] else None
             g_T = g_means if need[1] else None
         return (g_xyz, g_T, g_scaling, g_scales if need[3] else None, g_rotation, g_rots if need[5] else None,
-                g_opacity, None)
+                g_opacity, None, None)
 
 
 def _can_fuse_prepare(pc, d_xyz, d_rotation, d_scaling, is_6dof):
@@ -98,6 +130,30 @@ def _can_fuse_prepare(pc, d_xyz, d_rotation, d_scaling, is_6dof):
         if tuple(t.shape) != shp or t.dtype != torch.float32 or not t.is_cuda or not t.is_contiguous():
             return False
     return True
+
+
+def _grad_sinks(pc):
+    """The six .grad tensors FUSED_GRAD_ACCUMULATION adds into — (xyz, scaling, rotation, opacity, features_dc,
+    features_rest) — or None when `pc` does not qualify (then render() takes the autograd path)."""
+    if not (FUSED_GRAD_ACCUMULATION and torch.is_grad_enabled()):
+        return None
+    names = ("_xyz", "_scaling", "_rotation", "_opacity", "_features_dc", "_features_rest")
+    params = [getattr(pc, n, None) for n in names]
+    if not torch.is_tensor(params[0]):
+        return None
+    N = params[0].shape[0]
+    shapes = [(N, 3), (N, 3), (N, 4), (N, 1), (N, 1, 3), (N, 15, 3)]
+    for p, shp in zip(params, shapes):
+        if not torch.is_tensor(p) or not p.requires_grad or not p.is_leaf or tuple(p.shape) != shp:
+            return None
+        g = p.grad
+        if (g is None or g.dtype != torch.float32 or not g.is_contiguous() or g.device != p.device
+                or p.dtype != torch.float32 or not p.is_contiguous() or not p.is_cuda):
+            return None
+    rest = params[5]
+    if rest.data_ptr() % 16 or rest.grad.data_ptr() % 16 or getattr(pc, "max_sh_degree", 3) != 3:
+        return None
+    return tuple(p.grad for p in params)
 
 
 def eval_sh(deg, sh, dirs):
@@ -173,9 +229,12 @@ def render(viewpoint_camera, pc, pipe, bg_color, d_xyz, d_rotation, d_scaling, i
 
     fused = (not direct_compute and not getattr(pipe, "compute_cov3D_python", False)
              and _can_fuse_prepare(pc, d_xyz, d_rotation, d_scaling, is_6dof))
+    # (the SH-coefficient sinks need the rasterizer's SH path: not with the convert_SHs_python pipe flag)
+    sinks = _grad_sinks(pc) if (fused and not getattr(pipe, "convert_SHs_python", False)) else None
     if fused:
         means3D, opacity, scales, rotations = _PrepareGaussians.apply(
-            pc._xyz, d_xyz, pc._scaling, d_scaling, pc._rotation, d_rotation, pc._opacity, bool(is_6dof))
+            pc._xyz, d_xyz, pc._scaling, d_scaling, pc._rotation, d_rotation, pc._opacity, bool(is_6dof),
+            None if sinks is None else sinks[:4])
     elif direct_compute:
         means3D = d_xyz
     elif is_6dof:
@@ -205,7 +264,9 @@ def render(viewpoint_camera, pc, pipe, bg_color, d_xyz, d_rotation, d_scaling, i
         rotations = pc.get_rotation + d_rotation
 
     shs = colors_precomp = None
-    if colors_precomp is None:  # always true, as in the reference (:103)
+    if sinks is not None:
+        pass  # the rasterizer reads _features_dc / _features_rest in place: no `get_features` concatenation
+    elif colors_precomp is None:  # always true, as in the reference (:103)
         if getattr(pipe, "convert_SHs_python", False):
             feats = pc.get_features
             shs_view = feats.transpose(1, 2).view(-1, 3, (pc.max_sh_degree + 1) ** 2)
@@ -218,10 +279,16 @@ def render(viewpoint_camera, pc, pipe, bg_color, d_xyz, d_rotation, d_scaling, i
     else:
         colors_precomp = override_color
 
-    rendered_image, radii, depth = rasterizer(
-        means3D=means3D, means2D=screenspace_points, means2D_densify=screenspace_points_densify, shs=shs,
-        colors_precomp=colors_precomp, opacities=opacity, scales=scales, rotations=rotations,
-        cov3D_precomp=cov3D_precomp)
+    if sinks is not None:
+        # same rasterizer, SH coefficients read from (and their gradients added to) the two parameters in place
+        rendered_image, radii, depth = rasterize_gaussians(
+            means3D, screenspace_points, screenspace_points_densify, None, None, opacity, scales, rotations, None,
+            raster_settings, (pc._features_dc, pc._features_rest, sinks[4], sinks[5]))
+    else:
+        rendered_image, radii, depth = rasterizer(
+            means3D=means3D, means2D=screenspace_points, means2D_densify=screenspace_points_densify, shs=shs,
+            colors_precomp=colors_precomp, opacities=opacity, scales=scales, rotations=rotations,
+            cov3D_precomp=cov3D_precomp)
 
     return {"render": rendered_image,
             "viewspace_points": screenspace_points,

@@ -117,6 +117,29 @@ int d3g_raster_backward(const d3g_raster_settings* s, int32_t N, uint64_t pair_c
                         float* dL_dscales, float* dL_drotations, float* dL_dcov3D_precomp,
                         void* stream);
 
+/* The same two calls with the spherical-harmonics coefficients left in the reference's two parameters instead of
+ * the [N,16,3] tensor its `get_features` concatenates every frame (scene/gaussian_model.py:111-115:
+ * cat(_features_dc [N,1,3], _features_rest [N,15,3]); gaussian_renderer/__init__.py:112 passes the result as `shs`):
+ * the forward reads both tensors in place (no 19 MB copy per frame at 100k Gaussians), and the backward ADDS
+ * dL/d_features_dc and dL/d_features_rest to grad_features_dc / grad_features_rest — the parameters' .grad tensors,
+ * which must hold the running sums already (zeros before the first frame) — instead of writing a [N,16,3] tensor
+ * that autograd then splits and adds.  sh_coeffs must be 16 (max_sh_degree 3); features_rest and grad_features_rest
+ * must be 16-byte aligned.  Colours, clamp flags and every other gradient are bit-identical to the calls above. */
+int d3g_raster_preprocess_split(const d3g_raster_settings* s, int32_t N, const float* means3D,
+                                const float* features_dc, const float* features_rest, int32_t sh_coeffs,
+                                const float* opacities, const float* scales, const float* rotations,
+                                const float* cov3D_precomp, void* geom, int32_t* radii,
+                                uint32_t* num_rendered_host, void* stream);
+int d3g_raster_backward_split(const d3g_raster_settings* s, int32_t N, uint64_t pair_capacity,
+                              const float* means3D, const float* features_dc, const float* features_rest,
+                              int32_t sh_coeffs, const float* scales, const float* rotations,
+                              const float* cov3D_precomp, const int32_t* radii, void* geom, void* bin,
+                              void* img, const float* dL_dcolor, const float* dL_ddepth,
+                              float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dmeans2D_densify,
+                              float* grad_features_dc, float* grad_features_rest, float* dL_dopacities,
+                              float* dL_dscales, float* dL_drotations, float* dL_dcov3D_precomp,
+                              void* stream);
+
 /* Activation + deformation of the Gaussian parameters, fused (the elementwise work of
  * gaussian_renderer/__init__.py:69-97 and of the getters of scene/gaussian_model.py:58-78):
  *   means3D = xyz + d_xyz, or from_homogenous(d_xyz[N,4,4] . [xyz,1]) when is_6dof (utils/rigid_utils.py:86-107)
@@ -136,6 +159,16 @@ int d3g_gaussians_prepare_backward(int32_t N, int32_t is_6dof, const float* xyz,
                                    const float* g_scales_out, const float* g_rotations_out,
                                    float* g_xyz, float* g_dxyz_6dof, float* g_opacity,
                                    float* g_scaling, float* g_rotation, void* stream);
+/* Same, but the four parameter cotangents are ADDED to acc_xyz / acc_opacity / acc_scaling / acc_rotation (the
+ * parameters' .grad tensors holding the running sums; any may be NULL = not wanted) instead of being written to
+ * fresh tensors that autograd then adds to .grad one launch each.  acc_xyz receives g_means3D itself when not
+ * is_6dof.  g_dxyz_6dof (the cotangent handed on to the deformation network) is still written, not added. */
+int d3g_gaussians_prepare_backward_into(int32_t N, int32_t is_6dof, const float* xyz, const float* d_xyz,
+                                        const float* scaling, const float* rotation, const float* opacity,
+                                        const float* g_means3D, const float* g_opacity_out,
+                                        const float* g_scales_out, const float* g_rotations_out,
+                                        float* acc_xyz, float* g_dxyz_6dof, float* acc_opacity,
+                                        float* acc_scaling, float* acc_rotation, void* stream);
 
 /* Fused image loss of the training step (utils/loss_utils.py:18-19 l1_loss, :42-73 ssim with its 11x11 sigma-1.5
  * window, zero padding and C1/C2; combined as in train_baseline.py:126-127).  img, gt: [C,H,W] fp32 device.

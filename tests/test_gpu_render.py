@@ -301,3 +301,85 @@ def test_graphed_step_matches_eager_and_sees_optimizer_updates():
         assert not torch.equal(flat.flat, torch.zeros_like(flat.flat))
     finally:
         rast.PAIR_CAPACITY_POLICY = old_policy
+
+
+def _run_accumulating(g, cam, pipe, dev, deltas, is_6dof, sinks, init, frames=2, sh_degree=None):
+    """`frames` render + backward passes accumulating into pre-existing .grad tensors (copies of `init`)."""
+    renderer = pkg("renderer")
+    fired = []
+    renderer.FUSED_GRAD_ACCUMULATION = sinks
+    renderer.ON_GAUSSIAN_GRADS = (lambda: fired.append(1)) if sinks else None
+    if sh_degree is not None:
+        g.active_sh_degree = sh_degree
+    try:
+        for p, g0 in zip(g.parameters(), init):
+            p.grad = g0.clone()
+        for d in deltas:
+            d.grad = None
+        cot = pkg("synth").image_cotangent(cam.image_height, cam.image_width).to(dev)
+        for k in range(frames):
+            out = renderer.render(cam, g, pipe, torch.zeros(3, device=dev), deltas[0], deltas[1], deltas[2], is_6dof)
+            (out["render"] * cot * (1.0 + k)).sum().backward()
+        torch.cuda.synchronize()
+    finally:
+        renderer.FUSED_GRAD_ACCUMULATION = False
+        renderer.ON_GAUSSIAN_GRADS = None
+    st = pkg("rasterizer")._RasterizeGaussians.last_state     # colours (r,g,b,depth) and SH clamp flags of the last frame
+    out["_rgbd"], out["_clamped"] = st.read(3, torch.float32, 4 * st.N), st.read(7, torch.uint8, st.N)
+    return out, [p.grad.detach().clone() for p in g.parameters() + deltas], len(fired)
+
+
+@pytest.mark.parametrize("N,is_6dof,sh_degree", [(4000, False, 3), (4000, True, 3), (1003, False, 1), (37, False, 0),
+                                                 (20011, False, 2)])
+def test_fused_grad_accumulation_matches_autograd(N, is_6dof, sh_degree):
+    """renderer.FUSED_GRAD_ACCUMULATION: the backward kernels add the six Gaussian parameters' gradients into their
+    .grad tensors (SH coefficients read from _features_dc / _features_rest in place, no `get_features` concatenation,
+    scene/gaussian_model.py:111-115).  Image, radii, depth, per-Gaussian colours and clamp flags are bit-identical to
+    the autograd path; the accumulated gradients agree to fp32 summation-order noise, starting from non-zero .grad
+    tensors, over two frames, with a partial last warp (N not a multiple of 32) and at every SH degree.  The per-frame
+    callback fires once per frame."""
+    g, cam, pipe, dev = _scene(N, seed=21)
+    deltas = _deltas(N, dev, is_6dof)
+    gen = torch.Generator().manual_seed(77)
+    init = [(1e-4 * torch.randn(p.shape, generator=gen)).to(dev) for p in g.parameters()]
+    out_a, grads_a, fired_a = _run_accumulating(g, cam, pipe, dev, deltas, is_6dof, False, init, sh_degree=sh_degree)
+    out_s, grads_s, fired_s = _run_accumulating(g, cam, pipe, dev, deltas, is_6dof, True, init, sh_degree=sh_degree)
+    assert fired_a == 0 and fired_s == 2
+    assert torch.equal(out_a["radii"], out_s["radii"]) and int((out_s["radii"] > 0).sum()) > 0
+    assert torch.equal(out_a["render"], out_s["render"]) and torch.equal(out_a["depth"], out_s["depth"])
+    assert torch.equal(out_a["_rgbd"], out_s["_rgbd"]) and torch.equal(out_a["_clamped"], out_s["_clamped"])
+    names = ["xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation", "d_xyz", "d_rot", "d_scale"]
+    # (the per-Gaussian sums of the rasterizer backward land through atomics, so two runs differ by fp32 summation
+    #  order; the accumulation itself adds the same values in the same order)
+    for n, a, b, in zip(names, grads_a, grads_s):
+        assert _rel(b.cpu().numpy(), a.cpu().numpy()) < 1e-5, n
+    for n, a, b, g0 in zip(names, grads_a, grads_s, init):      # the part the two frames added, on its own scale
+        da, ds = (a - g0).cpu().numpy(), (b - g0).cpu().numpy()
+        if n == "f_rest" and sh_degree == 0:          # (degree 0 evaluates no higher-order coefficient)
+            assert np.abs(da).max() == 0 and np.abs(ds).max() == 0
+            continue
+        assert np.abs(da).max() > 0 and _rel(ds, da) < 1e-3, n
+    assert _rel(out_s["viewspace_points_densify"].grad.cpu().numpy(),
+                out_a["viewspace_points_densify"].grad.cpu().numpy()) < 1e-5
+
+
+def test_fused_grad_accumulation_falls_back_without_grad_tensors():
+    """The flag only applies when all six parameters already hold .grad tensors; otherwise render() silently takes
+    the autograd path (fresh .grad tensors appear as usual)."""
+    N = 2000
+    g, cam, pipe, dev = _scene(N, seed=22)
+    deltas = _deltas(N, dev, False)
+    renderer = pkg("renderer")
+    renderer.FUSED_GRAD_ACCUMULATION = True
+    try:
+        for p in g.parameters() + deltas:
+            p.grad = None
+        out = renderer.render(cam, g, pipe, torch.zeros(3, device=dev), deltas[0], deltas[1], deltas[2], False)
+        out["render"].sum().backward()
+        assert all(p.grad is not None for p in g.parameters())
+        with torch.no_grad():                       # and no_grad rendering never touches .grad
+            before = [p.grad.clone() for p in g.parameters()]
+            renderer.render(cam, g, pipe, torch.zeros(3, device=dev), deltas[0], deltas[1], deltas[2], False)
+        assert all(torch.equal(a, p.grad) for a, p in zip(before, g.parameters()))
+    finally:
+        renderer.FUSED_GRAD_ACCUMULATION = False

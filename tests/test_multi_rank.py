@@ -102,6 +102,53 @@ def test_uneven_shards_with_one_backward_per_step(tmp_path):
         assert torch.allclose(flat[8:10], params[1].grad, rtol=1e-6, atol=1e-6)
 
 
+def _worker_frame_callback(rank, world, port, T, out):
+    """renderer.FUSED_GRAD_ACCUMULATION's shape: the early parameters' gradients are added by kernels (here: by hand,
+    under no_grad — no AccumulateGrad, no hook) and the renderer reports each finished frame through
+    FlatGrads.on_frame_grads(); the early slice is reduced after the rank's last frame, uneven shards included."""
+    import importlib
+    import sys
+    sys.path.insert(0, ROOT)
+    frames = importlib.import_module(PKG + ".frames")
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.manual_seed(0)
+    params = [torch.randn(3, 2, requires_grad=True), torch.randn(2, requires_grad=True)]
+    fg = frames.FlatGrads(params, early=1)
+    mine = frames.shard_frames(T, world, rank)
+    fg.frames_per_exchange = len(mine)
+    results = []
+    for step in range(3):
+        fg.zero()
+        started = []
+        for k in mine:
+            gw, gb = torch.autograd.grad(_frame_loss(params, k), params)
+            with torch.no_grad():
+                params[0].grad += gw          # "kernel" accumulation of the early parameter
+                params[1].grad += gb
+            fg.on_frame_grads()
+            started.append(fg._work is not None)
+        assert started == [False] * (len(mine) - 1) + [True], started   # one early reduce, after the last frame
+        fg.all_reduce()
+        results.append(fg.flat.clone())
+    if rank == 0:
+        torch.save(results, out)
+    dist.destroy_process_group()
+
+
+def test_frame_callback_starts_the_early_reduce_once_per_step(tmp_path):
+    T, world = 3, 2
+    out = str(tmp_path / "r0.pt")
+    mp.spawn(_worker_frame_callback, args=(world, _free_port(), T, out), nprocs=world, join=True)
+    got = torch.load(out)
+    torch.manual_seed(0)
+    params = [torch.randn(3, 2, requires_grad=True), torch.randn(2, requires_grad=True)]
+    sum(_frame_loss(params, k) for k in range(T)).backward()
+    for flat in got:
+        assert torch.allclose(flat[:6].view(3, 2), params[0].grad, rtol=1e-6, atol=1e-6)
+        assert torch.allclose(flat[8:10], params[1].grad, rtol=1e-6, atol=1e-6)
+
+
 def test_shard_and_weights():
     import importlib
     frames = importlib.import_module(PKG + ".frames")
