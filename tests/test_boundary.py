@@ -70,3 +70,25 @@ def test_python_surface_mirrors_reference_names():
         assert hasattr(deform, name)
     assert list(inspect.signature(deform.DeformNetwork.__init__).parameters)[1:] == [
         "D", "W", "input_ch", "output_ch", "multires", "is_blender", "is_6dof"]
+
+
+def test_split_sh_entry_points_check_their_arguments_without_a_gpu():
+    """d3g_raster_preprocess_split / d3g_raster_backward_split refuse layouts they cannot read before any CUDA call:
+    only the reference's 1 + 15 coefficient split, 16-byte aligned _features_rest / its .grad."""
+    _lib = pkg("_lib")
+    lib = _lib.load()
+    s = _lib.RasterSettings()
+    s.image_height = s.image_width = 64
+    s.tanfovx = s.tanfovy = 0.5
+    s.bg = s.viewmatrix = s.projmatrix = s.campos = 256
+    s.scale_modifier, s.sh_degree = 1.0, 3
+    p, odd, null = C.c_void_p(256), C.c_void_p(260), C.c_void_p(0)
+    pre = lambda dc, rest, M: lib.d3g_raster_preprocess_split(C.byref(s), 10, p, dc, rest, M, p, p, p, null, p, p,
+                                                             null, null)
+    assert pre(p, p, 9) == -4 and b"sh_coeffs = 16" in lib.d3g_last_error()
+    assert pre(p, null, 16) == -1 and pre(null, p, 16) == -1
+    assert pre(p, odd, 16) == -1 and b"16-byte aligned" in lib.d3g_last_error()
+    bwd = lambda gdc, grest: lib.d3g_raster_backward_split(C.byref(s), 10, C.c_uint64(100), p, p, p, 16, p, p, null, p,
+                                                           p, p, p, p, null, p, p, p, gdc, grest, p, p, p, null, null)
+    assert bwd(null, p) == -1 and b"grad_features" in lib.d3g_last_error()
+    assert bwd(p, odd) == -1 and b"16-byte aligned" in lib.d3g_last_error()
